@@ -1,0 +1,144 @@
+/* include/rt_b200.h — C ABI of the B200-native path-tracing hot path.
+ *
+ * The reference (kouei/ray-tracing-in-one-weekend) has no FFI/plugin interface: its "API"
+ * is the set of C++ types used by main().  This header is the boundary a
+ * maintainer binds instead: plain pointers and sizes, no C++/torch types.  Each entry point
+ * names the reference code it replaces (paths relative to the reference root).
+ *
+ * Conventions: every function returns 0 on success or a negative RT_E_* code; the message
+ * of the last failure on the calling thread is rt_last_error().  Nothing ever calls exit()
+ * (the reference's checkCudaErrors does, src/gpu/cuda_utility.h:8-18).  Handles are not
+ * thread-safe; distinct handles may be used from distinct threads.  There is NO CPU
+ * fallback: without a CUDA device every compute entry point fails with RT_E_CUDA.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_OK 0
+#define RT_E_INVALID (-1) /* bad argument */
+#define RT_E_CUDA (-2)    /* CUDA runtime error / no device */
+#define RT_E_NOMEM (-3)
+#define RT_E_IO (-4)
+
+#define RT_LAMBERTIAN 0u /* src/cpu/material.h:14-34 */
+#define RT_METAL 1u      /* src/cpu/material.h:36-51 */
+#define RT_DIELECTRIC 2u /* src/cpu/material.h:53-87 */
+
+#define RT_SLICES 8u /* canonical sample slices per pixel (multi-GPU split) */
+
+/* One sphere with its material, in the reference's insertion order
+ * (hittable_list::add(make_shared<sphere>(center, radius, material)),
+ *  src/cpu/hittable_list.h:20, src/cpu/sphere.h:11-12).  radius keeps its sign
+ *  (negative = hollow bubble, archive/listing69/main.cc:61). */
+typedef struct rt_sphere {
+  double center[3];
+  double radius;
+  uint32_t kind;      /* RT_LAMBERTIAN | RT_METAL | RT_DIELECTRIC */
+  uint32_t _pad;
+  double albedo[3];   /* ignored for dielectric (attenuation is 1,1,1) */
+  double fuzz_or_ir;  /* metal: fuzz (clamped to <=1 like material.h:38); dielectric: ir */
+} rt_sphere;
+
+/* Exactly the constructor arguments of camera, src/cpu/camera.h:8-10. */
+typedef struct rt_camera {
+  double lookfrom[3], lookat[3], vup[3];
+  double vfov_deg, aspect_ratio, aperture, focus_dist;
+} rt_camera;
+
+/* Render parameters: the literals of main(), src/cpu/main.cc:82-86. */
+typedef struct rt_config {
+  uint32_t width, height;
+  uint32_t samples_per_pixel; /* total spp of the frame */
+  uint32_t max_depth;         /* 50 in the reference */
+  uint64_t seed;              /* frame seed of the Philox stream */
+  uint32_t sample_offset;     /* added to the sample index in the RNG key (progressive) */
+  uint32_t slice_begin, slice_end; /* canonical slices [begin,end) of RT_SLICES this call renders */
+  int32_t device;             /* CUDA device ordinal */
+  uint32_t flags;             /* RT_FLAG_* */
+} rt_config;
+
+#define RT_FLAG_COUNT_RAYS 1u /* fill rt_stats.rays (one atomic per work item) */
+
+typedef struct rt_stats {
+  uint64_t samples;      /* samples traced by this call */
+  uint64_t rays;         /* ray segments (ray_color invocations, src/cpu/main.cc:12) */
+  uint64_t sphere_tests; /* rays * sphere count (brute force) */
+  float render_ms;       /* device time of the path kernel (CUDA events) */
+  float finalize_ms;     /* device time of reduce+finalise */
+  uint32_t launches;     /* kernels launched by this call */
+  float frame_ms;        /* device time from the start of rt_render to the end of the finalise
+                            kernel on the frame's stream (set by rt_finalize) */
+} rt_stats;
+
+typedef struct rt_scene rt_scene;   /* device-resident flattened hittable_list */
+typedef struct rt_frame rt_frame;   /* device-resident accumulation buffers of one frame */
+
+const char *rt_last_error(void);
+/* Library/ABI version and the CUDA arch it was built for ("sm_100a"). */
+const char *rt_version(void);
+int rt_device_count(int *count);
+
+/* --- scene: replaces hittable_list + sphere + material objects (src/cpu/hittable_list.h,
+ *     sphere.h, material.h) and the GPU twin's new_world kernel (src/gpu/main.cu:18-75). */
+int rt_scene_create(const rt_sphere *spheres, uint32_t n, int32_t device, rt_scene **out);
+int rt_scene_destroy(rt_scene *);
+int rt_scene_count(const rt_scene *, uint32_t *n);
+
+/* --- frame: accumulation buffers [RT_SLICES][H][W] float4 on the device. */
+int rt_frame_create(uint32_t width, uint32_t height, int32_t device, rt_frame **out);
+int rt_frame_destroy(rt_frame *);
+/* Device pointer / byte size of the per-GPU partial sum (the pre-summed sub-tree of the
+ * slices this GPU rendered): [H][W] float4.  This is what crosses NVLink. */
+int rt_frame_partial_ptr(rt_frame *, void **dev_ptr, size_t *bytes);
+
+/* Run the frame's work on a caller-owned CUDA stream (a cudaStream_t; NULL = the frame's own
+ * stream) so that collectives and kernels order on one stream. */
+int rt_frame_set_stream(rt_frame *, void *cuda_stream);
+
+/* --- the hot path: replaces the pixel/sample loops + ray_color + everything below
+ *     (src/cpu/main.cc:12-30,111-123; GPU twin: render kernel, src/gpu/camera.h:169-195).
+ *     Renders slices [slice_begin, slice_end) of every pixel into the frame. */
+int rt_render(const rt_scene *, const rt_camera *, const rt_config *, rt_frame *, rt_stats *);
+
+/* Pre-sum this GPU's slices in the canonical pairwise tree into the partial buffer. */
+int rt_frame_reduce_local(rt_frame *, const rt_config *);
+
+/* Combine `count` partial buffers (device pointers on cfg->device, in rank order; count in
+ * {1,2,4,8}) with the upper levels of the same tree, then sum/spp -> sqrt -> clamp ->
+ * 8-bit (write_color, src/cpu/color.h:8-23).  rgb8_out is HOST memory [H][W][3], rows
+ * top->bottom; linear_out (optional, HOST, [H][W][3] float) receives the linear sums. */
+int rt_finalize(rt_frame *, const rt_config *, const void *const *partials, uint32_t count,
+                uint8_t *rgb8_out, float *linear_out, rt_stats *);
+
+/* Convenience: render all slices on one GPU + reduce + finalise (host buffers out). */
+int rt_render_image(const rt_scene *, const rt_camera *, const rt_config *, uint8_t *rgb8_out,
+                    float *linear_out, rt_stats *);
+
+/* --- accuracy gate: pixel-centre, zero-lens primary rays, closest hit in reference order
+ *     (hittable_list::hit + sphere::hit, src/cpu/hittable_list.h:28-43, sphere.h:24-51).
+ *     use_f64 = 1: IEEE double without FMA contraction, op-for-op like the reference
+ *     (ids bit-exact, normals <= 2 ulp); use_f64 = 0: the production f32 intersection.
+ *     Outputs are HOST arrays, rows top->bottom; t/normal are double in both modes. */
+int rt_primary_hits(const rt_scene *, const rt_camera *, uint32_t width, uint32_t height,
+                    int32_t device, int use_f64, int32_t *ids, double *t, double *normal,
+                    uint8_t *front_face);
+
+/* --- measurement aid: sustained FP32 FFMA throughput of the device (TFLOP/s, FMA = 2),
+ *     measured with a register-resident micro-kernel; the roofline denominator of bench.py. */
+int rt_measure_fp32_peak(int32_t device, float *tflops, float *sm_clock_mhz_est);
+
+/* --- output: P3 text, rows top->bottom, "r g b\n" per pixel (src/cpu/main.cc:109,
+ *     color.h:20-22). */
+int rt_write_ppm(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,262 @@
+"""rt_b200 — ctypes binding of the C ABI in include/rt_b200.h (librt_b200.so).
+
+This is test/bench plumbing around the product library, shaped like the reference's own
+vocabulary (spheres with lambertian/metal/dielectric materials, a camera built from
+lookfrom/lookat/vup/vfov/aspect/aperture/focus_dist, src/cpu/main.cc:93-99).  There is no
+CPU fallback: if librt_b200.so is missing, importing the binding raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+
+LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
+SLICES = 8
+FLAG_COUNT_RAYS = 1
+
+
+class RtError(RuntimeError):
+    pass
+
+
+class _Sphere(C.Structure):
+    _fields_ = [("center", C.c_double * 3), ("radius", C.c_double), ("kind", C.c_uint32),
+                ("_pad", C.c_uint32), ("albedo", C.c_double * 3), ("fuzz_or_ir", C.c_double)]
+
+
+class _Camera(C.Structure):
+    _fields_ = [("lookfrom", C.c_double * 3), ("lookat", C.c_double * 3), ("vup", C.c_double * 3),
+                ("vfov_deg", C.c_double), ("aspect_ratio", C.c_double), ("aperture", C.c_double),
+                ("focus_dist", C.c_double)]
+
+
+class _Config(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("samples_per_pixel", C.c_uint32),
+                ("max_depth", C.c_uint32), ("seed", C.c_uint64), ("sample_offset", C.c_uint32),
+                ("slice_begin", C.c_uint32), ("slice_end", C.c_uint32), ("device", C.c_int32),
+                ("flags", C.c_uint32)]
+
+
+class _Stats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("rays", C.c_uint64), ("sphere_tests", C.c_uint64),
+                ("render_ms", C.c_float), ("finalize_ms", C.c_float), ("launches", C.c_uint32),
+                ("frame_ms", C.c_float)]
+
+
+# every symbol include/rt_b200.h declares
+SYMBOLS = [
+    "rt_last_error", "rt_version", "rt_device_count", "rt_scene_create", "rt_scene_destroy",
+    "rt_scene_count", "rt_frame_create", "rt_frame_destroy", "rt_frame_partial_ptr", "rt_render",
+    "rt_frame_reduce_local", "rt_finalize", "rt_render_image", "rt_primary_hits", "rt_write_ppm",
+    "rt_frame_set_stream", "rt_measure_fp32_peak",
+]
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load librt_b200.so (fails loudly when it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RtError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; "
+                          "g.build()'` (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.rt_last_error.restype = C.c_char_p
+        L.rt_version.restype = C.c_char_p
+        for name in SYMBOLS[2:]:
+            getattr(L, name).restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise RtError(f"rt_b200 error {rc}: {lib().rt_last_error().decode()}")
+
+
+@dataclass
+class Camera:
+    """camera(lookfrom, lookat, vup, vfov, aspect_ratio, aperture, focus_dist), camera.h:8-10"""
+    lookfrom: tuple = (13.0, 2.0, 3.0)
+    lookat: tuple = (0.0, 0.0, 0.0)
+    vup: tuple = (0.0, 1.0, 0.0)
+    vfov: float = 20.0
+    aspect_ratio: float = 16.0 / 9.0
+    aperture: float = 0.1
+    focus_dist: float = 10.0
+
+    def c(self) -> _Camera:
+        return _Camera((C.c_double * 3)(*self.lookfrom), (C.c_double * 3)(*self.lookat),
+                       (C.c_double * 3)(*self.vup), self.vfov, self.aspect_ratio, self.aperture,
+                       self.focus_dist)
+
+
+@dataclass
+class Config:
+    width: int
+    height: int
+    samples_per_pixel: int
+    max_depth: int = 50
+    seed: int = 0
+    sample_offset: int = 0
+    slice_begin: int = 0
+    slice_end: int = SLICES
+    device: int = 0
+    flags: int = 0
+
+    def c(self) -> _Config:
+        return _Config(self.width, self.height, self.samples_per_pixel, self.max_depth, self.seed,
+                       self.sample_offset, self.slice_begin, self.slice_end, self.device, self.flags)
+
+
+@dataclass
+class Stats:
+    samples: int = 0
+    rays: int = 0
+    sphere_tests: int = 0
+    render_ms: float = 0.0
+    finalize_ms: float = 0.0
+    launches: int = 0
+    frame_ms: float = 0.0
+
+    @staticmethod
+    def of(s: _Stats) -> "Stats":
+        return Stats(s.samples, s.rays, s.sphere_tests, s.render_ms, s.finalize_ms, s.launches,
+                     s.frame_ms)
+
+
+def spheres_from_rows(rows: np.ndarray):
+    """[n][9] f64 rows (cx cy cz radius kind r g b fuzz|ir — the oracle's scene dump layout,
+    reference insertion order) -> ctypes rt_sphere array."""
+    rows = np.ascontiguousarray(rows, dtype=np.float64).reshape(-1, 9)
+    arr = (_Sphere * max(len(rows), 1))()
+    for k, r in enumerate(rows):
+        arr[k].center[:] = r[0:3]
+        arr[k].radius = r[3]
+        arr[k].kind = int(r[4])
+        arr[k].albedo[:] = r[5:8]
+        arr[k].fuzz_or_ir = r[8]
+    return arr, len(rows)
+
+
+class Scene:
+    """Device-resident flattened hittable_list (src/cpu/hittable_list.h)."""
+
+    def __init__(self, rows: np.ndarray, device: int = 0):
+        arr, n = spheres_from_rows(rows)
+        self.n, self.device = n, device
+        self._h = C.c_void_p()
+        _check(lib().rt_scene_create(arr, C.c_uint32(n), C.c_int32(device), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().rt_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Frame:
+    """Per-GPU accumulation buffers of one frame."""
+
+    def __init__(self, width: int, height: int, device: int = 0):
+        self.width, self.height, self.device = width, height, device
+        self._h = C.c_void_p()
+        _check(lib().rt_frame_create(C.c_uint32(width), C.c_uint32(height), C.c_int32(device),
+                                     C.byref(self._h)))
+
+    def set_stream(self, cuda_stream: int | None) -> None:
+        _check(lib().rt_frame_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
+
+    def partial_ptr(self):
+        p, nbytes = C.c_void_p(), C.c_size_t()
+        _check(lib().rt_frame_partial_ptr(self._h, C.byref(p), C.byref(nbytes)))
+        return p.value, nbytes.value
+
+    def render(self, scene: Scene, cam: Camera, cfg: Config) -> Stats:
+        st, cc, cf = _Stats(), cam.c(), cfg.c()
+        _check(lib().rt_render(scene._h, C.byref(cc), C.byref(cf), self._h, C.byref(st)))
+        return Stats.of(st)
+
+    def reduce_local(self, cfg: Config) -> None:
+        cf = cfg.c()
+        _check(lib().rt_frame_reduce_local(self._h, C.byref(cf)))
+
+    def finalize(self, cfg: Config, partial_ptrs=None, want_linear=False, rgb_out=None,
+                 linear_out=None):
+        """-> (rgb8 [H][W][3] uint8, linear [H][W][3] float32 | None, Stats)"""
+        if partial_ptrs is None:
+            partial_ptrs = [self.partial_ptr()[0]]
+        n = len(partial_ptrs)
+        ptrs = (C.c_void_p * n)(*partial_ptrs)
+        rgb = rgb_out if rgb_out is not None else np.empty((self.height, self.width, 3), np.uint8)
+        lin = linear_out
+        if lin is None and want_linear:
+            lin = np.empty((self.height, self.width, 3), np.float32)
+        st, cf = _Stats(), cfg.c()
+        _check(lib().rt_finalize(self._h, C.byref(cf), ptrs, C.c_uint32(n),
+                                 C.c_void_p(rgb.ctypes.data),
+                                 C.c_void_p(lin.ctypes.data) if lin is not None else None,
+                                 C.byref(st)))
+        return rgb, lin, Stats.of(st)
+
+    def close(self):
+        if self._h:
+            lib().rt_frame_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def render_image(scene: Scene, cam: Camera, cfg: Config, want_linear=True):
+    """One-call render on one GPU -> (rgb8, linear sums, Stats)."""
+    rgb = np.empty((cfg.height, cfg.width, 3), np.uint8)
+    lin = np.empty((cfg.height, cfg.width, 3), np.float32) if want_linear else None
+    st, cc, cf = _Stats(), cam.c(), cfg.c()
+    _check(lib().rt_render_image(scene._h, C.byref(cc), C.byref(cf), C.c_void_p(rgb.ctypes.data),
+                                 C.c_void_p(lin.ctypes.data) if lin is not None else None,
+                                 C.byref(st)))
+    return rgb, lin, Stats.of(st)
+
+
+def primary_hits(scene: Scene, cam: Camera, width: int, height: int, use_f64: bool, device=0):
+    """-> ids int32 [H][W], t f64 [H][W], normal f64 [H][W][3], front_face u8 [H][W]"""
+    ids = np.empty((height, width), np.int32)
+    t = np.empty((height, width), np.float64)
+    nrm = np.empty((height, width, 3), np.float64)
+    ff = np.empty((height, width), np.uint8)
+    cc = cam.c()
+    _check(lib().rt_primary_hits(scene._h, C.byref(cc), C.c_uint32(width), C.c_uint32(height),
+                                 C.c_int32(device), C.c_int(1 if use_f64 else 0),
+                                 C.c_void_p(ids.ctypes.data), C.c_void_p(t.ctypes.data),
+                                 C.c_void_p(nrm.ctypes.data), C.c_void_p(ff.ctypes.data)))
+    return ids, t, nrm, ff
+
+
+def measure_fp32_peak(device: int = 0):
+    """-> (TFLOP/s of back-to-back FFMA, estimated SM clock in MHz)"""
+    tf, mhz = C.c_float(), C.c_float()
+    _check(lib().rt_measure_fp32_peak(C.c_int32(device), C.byref(tf), C.byref(mhz)))
+    return tf.value, mhz.value
+
+
+def write_ppm(path: str, rgb8: np.ndarray) -> None:
+    h, w, _ = rgb8.shape
+    rgb8 = np.ascontiguousarray(rgb8, np.uint8)
+    _check(lib().rt_write_ppm(path.encode(), C.c_void_p(rgb8.ctypes.data), C.c_uint32(w),
+                              C.c_uint32(h)))

@@ -1,0 +1,57 @@
+// csrc/rt_kernels.h — host-visible launch interface of the kernels (internal to the .so).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_device.cuh"
+
+#define RT_SLICES_DEV 8u
+
+namespace rtb {
+
+struct PathParams {
+  SceneView scene;
+  CameraF32 cam;
+  uint32_t width, height;
+  uint32_t spp, max_depth;
+  uint64_t seed;
+  uint32_t sample_offset;
+  uint32_t slice_begin, slice_end;
+  float4 *accum;                 // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
+  unsigned long long *counter;   // work-queue head (zeroed before launch)
+};
+
+struct PathLaunchInfo {
+  int rays_per_lane, grid, block, blocks_per_sm;
+  size_t smem_bytes;
+  bool scene_in_smem;
+};
+
+// rays_per_lane: 1, 2 or 4 (0 = default).  Launches the persistent path kernel.
+cudaError_t launch_path(const PathParams &p, int rays_per_lane, int sm_count,
+                        size_t smem_optin_max, cudaStream_t st, PathLaunchInfo *info);
+
+// dst[i] = canonical sub-tree sum of slices [slice_begin, slice_end) (aligned power of 2).
+cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t slice_begin,
+                                uint32_t slice_end, float4 *dst, int sm_count, cudaStream_t st);
+
+// partials: `count` device pointers (count in {1,2,4,8}) in rank order.
+cudaError_t launch_finalize(const float4 *const *partials, uint32_t count, uint32_t npix,
+                            float scale, uint32_t *rgb_words, float *linear,
+                            unsigned long long *rays, int sm_count, cudaStream_t st);
+
+cudaError_t launch_primary_f32(const SceneView &sc, const CameraF32 &cam, uint32_t W, uint32_t H,
+                               int32_t *ids, double *t, double *normal, uint8_t *ff,
+                               cudaStream_t st);
+
+// FFMA throughput micro-kernel: blocks x 256 threads x iters x 64 FFMA.  out: blocks*256 floats.
+cudaError_t launch_ffma_peak(float *out, int blocks, int iters, long long *cycles,
+                             cudaStream_t st);
+
+// rt_primary_f64.cu (compiled with -fmad=false): op-for-op IEEE double gate kernel.
+cudaError_t launch_primary_f64(const double4 *exact, uint32_t n, const CameraF64 &cam, uint32_t W,
+                               uint32_t H, int32_t *ids, double *t, double *normal, uint8_t *ff,
+                               cudaStream_t st);
+
+}  // namespace rtb
