@@ -1,0 +1,55 @@
+#!/usr/bin/env python
+"""Render one frame through the C ABI and print the stats (used under ncu / for quick A-B runs).
+
+    python tools/run_once.py --scene cover --w 1200 --h 675 --spp 64 [--reps 3] [--ppm out.ppm]
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from __graft_entry__ import _load_pkg  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--scene", default="cover", choices=["cover", "three"])
+    ap.add_argument("--w", type=int, default=1200)
+    ap.add_argument("--h", type=int, default=675)
+    ap.add_argument("--spp", type=int, default=64)
+    ap.add_argument("--depth", type=int, default=50)
+    ap.add_argument("--reps", type=int, default=1)
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--ppm", default=None)
+    a = ap.parse_args()
+    rt = _load_pkg()
+    rows = np.load(os.path.join(ROOT, "tests", "golden", f"{a.scene}_small.npz"))["spheres"]
+    if a.scene == "cover":
+        cam = rt.Camera(aspect_ratio=a.w / a.h)
+    else:
+        cam = rt.Camera((3.0, 3.0, 2.0), (0.0, 0.0, -1.0), (0.0, 1.0, 0.0), 20.0, a.w / a.h, 2.0,
+                        float(np.sqrt(27.0)))
+    scene = rt.Scene(rows)
+    frame = rt.Frame(a.w, a.h)
+    cfg = rt.Config(a.w, a.h, a.spp, a.depth, seed=a.seed)
+    for _ in range(a.reps):
+        st = frame.render(scene, cam, cfg)
+        frame.reduce_local(cfg)
+        rgb, _, fin = frame.finalize(cfg)
+        tests = fin.rays * len(rows)
+        print(json.dumps({
+            "render_ms": st.render_ms, "finalize_ms": fin.finalize_ms, "samples": st.samples,
+            "rays": fin.rays, "msamples_s": st.samples / st.render_ms / 1e3,
+            "mrays_s": fin.rays / st.render_ms / 1e3,
+            "tflops_algorithmic": tests * 17 / (st.render_ms * 1e-3) / 1e12}))
+    if a.ppm:
+        rt.write_ppm(a.ppm, rgb)
+
+
+if __name__ == "__main__":
+    main()
