@@ -14,7 +14,8 @@ from dataclasses import dataclass, field
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+# RT_B200_LIB selects an experimental build of the same library (kernel A/B runs)
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
 SLICES = 8

@@ -38,7 +38,8 @@ struct rt_scene {
   float4 *fast;
   double4 *exact;
   float4 *mat;
-  uint8_t *kind;
+  float2 *aux;
+  uint32_t n_pad;
 };
 
 struct rt_frame {
@@ -72,10 +73,13 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
   *out = nullptr;
   if (n && !sp) return fail(RT_E_INVALID, "spheres is NULL");
   if (n > (1u << 24)) return fail(RT_E_INVALID, "too many spheres (%u)", n);
-  std::vector<float4> fast(n ? n : 1);
-  std::vector<double4> exact(n ? n : 1);
-  std::vector<float4> mat(n ? n : 1);
-  std::vector<uint8_t> kind(n ? n : 1);
+  // rows are padded to a multiple of 4 (the filter loop is unrolled by 4); a padding row has
+  // w = -inf so that b*b + q = -inf never reaches the threshold
+  const uint32_t npad = n ? (n + 3u) & ~3u : 4u;
+  std::vector<float4> fast(npad, make_float4(0.f, 0.f, 0.f, -INFINITY));
+  std::vector<double4> exact(npad, make_double4(0, 0, 0, 1));
+  std::vector<float4> mat(npad, make_float4(0.f, 0.f, 0.f, 0.f));
+  std::vector<float2> aux(npad, make_float2(1.f, 0.f));
   for (uint32_t k = 0; k < n; ++k) {
     const rt_sphere &s = sp[k];
     if (s.kind > RT_DIELECTRIC) return fail(RT_E_INVALID, "sphere %u: bad material kind %u", k, s.kind);
@@ -100,25 +104,28 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
     else
       mat[k] = make_float4((float)s.albedo[0], (float)s.albedo[1], (float)s.albedo[2],
                            s.kind == RT_METAL ? (float)param : 0.f);
-    kind[k] = (uint8_t)s.kind;
+    uint32_t kind_bits = s.kind;
+    float kind_f;
+    memcpy(&kind_f, &kind_bits, 4);
+    aux[k] = make_float2((float)(1.0 / r), kind_f);
   }
   CU(cudaSetDevice(device));
   rt_scene *sc = new (std::nothrow) rt_scene();
   if (!sc) return fail(RT_E_NOMEM, "out of host memory");
-  sc->device = device; sc->n = n;
-  size_t m = n ? n : 1;
+  sc->device = device; sc->n = n; sc->n_pad = npad;
+  size_t m = npad;
   cudaError_t e;
   if ((e = cudaMalloc(&sc->fast, m * sizeof(float4))) != cudaSuccess ||
       (e = cudaMalloc(&sc->exact, m * sizeof(double4))) != cudaSuccess ||
       (e = cudaMalloc(&sc->mat, m * sizeof(float4))) != cudaSuccess ||
-      (e = cudaMalloc(&sc->kind, m)) != cudaSuccess) {
+      (e = cudaMalloc(&sc->aux, m * sizeof(float2))) != cudaSuccess) {
     rt_scene_destroy(sc);
     return fail(RT_E_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
   }
   CU(cudaMemcpy(sc->fast, fast.data(), m * sizeof(float4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->exact, exact.data(), m * sizeof(double4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->mat, mat.data(), m * sizeof(float4), cudaMemcpyHostToDevice));
-  CU(cudaMemcpy(sc->kind, kind.data(), m, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(sc->aux, aux.data(), m * sizeof(float2), cudaMemcpyHostToDevice));
   *out = sc;
   return RT_OK;
 }
@@ -126,7 +133,7 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
 extern "C" int rt_scene_destroy(rt_scene *sc) {
   if (!sc) return RT_OK;
   cudaSetDevice(sc->device);
-  cudaFree(sc->fast); cudaFree(sc->exact); cudaFree(sc->mat); cudaFree(sc->kind);
+  cudaFree(sc->fast); cudaFree(sc->exact); cudaFree(sc->mat); cudaFree(sc->aux);
   delete sc;
   return RT_OK;
 }
@@ -139,7 +146,7 @@ extern "C" int rt_scene_count(const rt_scene *sc, uint32_t *n) {
 
 static SceneView view_of(const rt_scene *sc) {
   SceneView v;
-  v.fast = sc->fast; v.exact = sc->exact; v.mat = sc->mat; v.kind = sc->kind; v.n = sc->n;
+  v.fast = sc->fast; v.exact = sc->exact; v.mat = sc->mat; v.aux = sc->aux; v.n = sc->n; v.n_pad = sc->n_pad;
   return v;
 }
 
@@ -199,7 +206,7 @@ static CameraF32 narrow_camera(const CamFrame &f, uint32_t W, uint32_t H) {
 extern "C" int rt_frame_create(uint32_t width, uint32_t height, int32_t device, rt_frame **out) {
   if (!out) return fail(RT_E_INVALID, "out is NULL");
   *out = nullptr;
-  if (width < 2 || height < 2 || (uint64_t)width * height > (1ull << 28))
+  if (width < 2 || height < 2 || (uint64_t)width * height >= (1ull << 28))
     return fail(RT_E_INVALID, "image size %ux%u out of range (min 2x2)", width, height);
   CU(cudaSetDevice(device));
   rt_frame *f = new (std::nothrow) rt_frame();

@@ -10,11 +10,13 @@ namespace rtb {
 // ---------------------------------------------------------------- flattened scene (HBM)
 // hittable_list (src/cpu/hittable_list.h:12-26) flattened in insertion order.
 struct SceneView {
-  const float4 *fast;    // [n] {cx, cy, cz, r^2-|c|^2 + slack}  conservative f32 filter row
-  const double4 *exact;  // [n] {cx, cy, cz, signed radius}       f64 candidate resolution
+  const float4 *fast;    // [n_pad] {cx, cy, cz, r^2-|c|^2 + slack}  conservative f32 filter row
+  const double4 *exact;  // [n_pad] {cx, cy, cz, signed radius}       f64 candidate resolution
   const float4 *mat;     // [n] {albedo.r, albedo.g, albedo.b, fuzz | ir}
-  const uint8_t *kind;   // [n] RT_LAMBERTIAN | RT_METAL | RT_DIELECTRIC
-  uint32_t n;
+  const float2 *aux;     // [n] {1 / signed radius, material kind (integer bits)}
+  uint32_t n;            // spheres in the hittable_list
+  uint32_t n_pad;        // rows allocated: n rounded up to a multiple of 4; padding rows can
+                         // never pass the filter (w = -inf)
 };
 
 // camera (src/cpu/camera.h:8-26) derived on the host in f64, narrowed once.

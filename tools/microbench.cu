@@ -85,17 +85,157 @@ void run(const char *name, int sms, int blocks_per_sm) {
   cudaFree(out); cudaFree(cyc); free(h);
 }
 
+
+// ---- sphere-row feed variants: one {x,y,z,w} row per NP*7 FFMA2, rows from shared memory
+// (broadcast LDS.128) or from the constant bank through uniform registers (LDCU).
+__device__ __forceinline__ float2 bc(float v) { return make_float2(v, v); }
+__constant__ float4 c_rows[512];
+__constant__ float c_w[512];
+
+template <int NP, bool CONSTANT>
+__global__ void __launch_bounds__(256) feed(float *out, int iters, const float4 *g_rows, float thr) {
+  __shared__ float4 s_rows[512];
+  for (int k = threadIdx.x; k < 512; k += 256) s_rows[k] = g_rows[k];
+  __syncthreads();
+  float2 D0[NP], D1[NP], D2[NP], N0[NP], O0[NP], O1[NP], O2[NP];
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    float t = (float)(threadIdx.x + p) * 1e-3f;
+    D0[p] = make_float2(t, t + 1); D1[p] = make_float2(t + 2, t + 3); D2[p] = make_float2(t + 4, t + 5);
+    N0[p] = make_float2(t, -t); O0[p] = make_float2(t * 2, t * 3); O1[p] = make_float2(t * 4, t * 5);
+    O2[p] = make_float2(t * 6, t * 7);
+  }
+  int cnt = 0;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll 4
+    for (int s = 0; s < 512; ++s) {
+      float4 S = CONSTANT ? c_rows[s] : s_rows[s];
+      bool any = false;
+      if (CONSTANT) {  // x,y,z stay in uniform registers; w comes from its own array into a vector register
+        S.w = c_w[s];
+        asm volatile("" : "+f"(S.w));
+      }
+#pragma unroll
+      for (int p = 0; p < NP; ++p) {
+        float2 b = ffma2(bc(S.x), D0[p], ffma2(bc(S.y), D1[p], ffma2(bc(S.z), D2[p], N0[p])));
+        float2 q = ffma2(bc(S.x), O0[p], ffma2(bc(S.y), O1[p], ffma2(bc(S.z), O2[p], bc(S.w))));
+        float2 e = ffma2(b, b, q);
+        any = any || e.x >= thr || e.y >= thr;
+      }
+      if (any) cnt += s;
+    }
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = (float)cnt;
+}
+
+template <int NP, bool CONSTANT>
+void run_feed(const char *name, int sms, int blocks_per_sm) {
+  int blocks = sms * blocks_per_sm, iters = 40;
+  float *out; float4 *rows;
+  CK(cudaMalloc(&out, (size_t)blocks * 256 * 4));
+  CK(cudaMalloc(&rows, 512 * 16));
+  float4 h[512];
+  for (int k = 0; k < 512; ++k) h[k] = make_float4(k * 1e-3f, 1.f - k * 1e-3f, 0.5f, -1e30f);
+  CK(cudaMemcpy(rows, h, sizeof h, cudaMemcpyHostToDevice));
+  CK(cudaMemcpyToSymbol(c_rows, h, sizeof h));
+  float hw[512];
+  for (int k = 0; k < 512; ++k) hw[k] = h[k].w;
+  CK(cudaMemcpyToSymbol(c_w, hw, sizeof hw));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    CK(cudaEventRecord(e0));
+    feed<NP, CONSTANT><<<blocks, 256>>>(out, iters, rows, 1e30f);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep && ms < best) best = ms;
+  }
+  double fma = 14.0 * NP * 512.0 * iters * 256.0 * blocks;
+  printf("%-34s %2d blk/SM  %7.2f TFLOP/s  (%.3f ms)\n", name, blocks_per_sm, 2.0 * fma / (best * 1e-3) / 1e12, best);
+  cudaFree(out); cudaFree(rows);
+}
+
+
+// ---- register-file pressure: every FMA reads three DISTINCT register operands per lane.
+// V=0: scalar FFMA d=a*b+c (3 reads).  V=1: FFMA2 with three pair operands (6 reads / 2 FMA).
+// V=2: FFMA2 with a scalar-broadcast multiplier (.F32) (5 reads).  V=3: FFMA2 with the
+// multiplier in a uniform register (4 reads).
+template <int V>
+__global__ void __launch_bounds__(256) rfbench(float *out, int iters, const float *g, float u0) {
+  float2 a[8], b[8], c[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    a[k] = make_float2(g[threadIdx.x + k], g[threadIdx.x + k + 8]);
+    b[k] = make_float2(g[threadIdx.x + k + 16], g[threadIdx.x + k + 24]);
+    c[k] = make_float2(g[threadIdx.x + k + 32], g[threadIdx.x + k + 40]);
+  }
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int k1 = (k + 1 + u) & 7, k2 = (k + 3 + u) & 7;
+        if (V == 0) { a[k].x = fmaf(b[k1].x, c[k2].x, a[k].x); a[k].y = fmaf(b[k1].y, c[k2].y, a[k].y); }
+        if (V == 1) a[k] = ffma2(b[k1], c[k2], a[k]);
+        if (V == 2) a[k] = ffma2(bc(b[k1].x), c[k2], a[k]);
+        if (V == 3) a[k] = ffma2(bc(u0), c[k2], a[k]);
+      }
+    }
+  }
+  float s = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += a[k].x + a[k].y;
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <int V>
+void run_rf(const char *name, int sms, int blocks_per_sm) {
+  int blocks = sms * blocks_per_sm, iters = 5000;
+  float *out, *g;
+  CK(cudaMalloc(&out, (size_t)blocks * 256 * 4));
+  CK(cudaMalloc(&g, 1024 * 4));
+  CK(cudaMemset(g, 0, 1024 * 4));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    CK(cudaEventRecord(e0));
+    rfbench<V><<<blocks, 256>>>(out, iters, g, 0.5f);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep && ms < best) best = ms;
+  }
+  double fma = 16.0 * 4 * iters * 256.0 * blocks;
+  printf("%-44s %2d blk/SM  %7.2f TFLOP/s  (%.3f ms)\n", name, blocks_per_sm, 2.0 * fma / (best * 1e-3) / 1e12, best);
+  cudaFree(out); cudaFree(g);
+}
+
 int main() {
   cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, 0));
   int sms = p.multiProcessorCount;
   printf("%s, %d SMs\n", p.name, sms);
-  for (int bps : {2, 4, 8}) {
+  for (int bps : {8}) {
     run<0>("FFMA x14", sms, bps);
     run<1>("FFMA2 x7", sms, bps);
     run<4>("FFMA x14 + 2 FSETP", sms, bps);
     run<2>("FFMA2 x7 + 2 FSETP", sms, bps);
     run<3>("FFMA2 x7 + 2 FSETP + LDS.128", sms, bps);
     run<5>("FFMA2 x7 + 2 FMNMX", sms, bps);
+  }
+  for (int bps : {2, 4}) {
+    run_rf<0>("FFMA  3 distinct reg operands", sms, bps);
+    run_rf<1>("FFMA2 3 distinct pair operands", sms, bps);
+    run_rf<2>("FFMA2 scalar-broadcast multiplier (.F32 R)", sms, bps);
+    run_rf<3>("FFMA2 uniform-register multiplier (.F32 UR)", sms, bps);
+  }
+  for (int bps : {2, 4}) {
+    run_feed<1, false>("filter R=2 rows via LDS.128", sms, bps);
+    run_feed<1, true>("filter R=2 rows via LDCU", sms, bps);
+    run_feed<2, false>("filter R=4 rows via LDS.128", sms, bps);
+    run_feed<2, true>("filter R=4 rows via LDCU", sms, bps);
   }
   return 0;
 }
