@@ -28,8 +28,8 @@ namespace rtb {
 #endif
 
 constexpr int kBlock = 256;
-constexpr int kCandCap = 8;
-constexpr int kGroup = 4;    // sphere rows per filter group (scene rows are padded to this)  // candidate list capacity per slot before an in-loop flush
+constexpr int kCandCap = 8;  // candidate list capacity per slot before an in-loop flush
+constexpr int kGroup = 4;    // sphere rows per filter group (scene rows are padded to this)
 
 // ---------------------------------------------------------------- packed f32x2 helpers
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
@@ -112,11 +112,12 @@ path_kernel(const __grid_constant__ PathParams P) {
   const uint32_t tid = threadIdx.x;
 
   // ---- shared memory carve-up (scene part only when SMEM)
-  const size_t scene_bytes = SMEM ? (size_t)npad * 72 : 0;
-  float4 *s_fast = reinterpret_cast<float4 *>(smem_raw);
-  double4 *s_exact = reinterpret_cast<double4 *>(smem_raw + (size_t)npad * 16);
-  float4 *s_mat = reinterpret_cast<float4 *>(smem_raw + (size_t)npad * 48);
-  float2 *s_aux = reinterpret_cast<float2 *>(smem_raw + (size_t)npad * 64);
+  const size_t scene_bytes = SMEM ? (size_t)npad * 72 + kGroup * 16 : 0;
+  // [exact npad*32][mat npad*16][aux npad*8][fast (npad + kGroup)*16]
+  double4 *s_exact = reinterpret_cast<double4 *>(smem_raw);
+  float4 *s_mat = reinterpret_cast<float4 *>(smem_raw + (size_t)npad * 32);
+  float2 *s_aux = reinterpret_cast<float2 *>(smem_raw + (size_t)npad * 48);
+  float4 *s_fast = reinterpret_cast<float4 *>(smem_raw + (size_t)npad * 56);
   uint32_t *s_cand = reinterpret_cast<uint32_t *>(smem_raw + scene_bytes);
   double *s_hit_n = reinterpret_cast<double *>(smem_raw + scene_bytes +
                                                (size_t)R * kCandCap * kBlock * 4);
@@ -135,7 +136,7 @@ path_kernel(const __grid_constant__ PathParams P) {
     if (tid == 0) mbar_init(&s_bar, 1);
     __syncthreads();
     if (tid == 0) {
-      mbar_expect_tx(&s_bar, npad * 72u);
+      mbar_expect_tx(&s_bar, npad * 72u + kGroup * 16u);
       const uint32_t kChunk = 32768u;
       const unsigned char *src[4] = {reinterpret_cast<const unsigned char *>(P.scene.fast),
                                      reinterpret_cast<const unsigned char *>(P.scene.exact),
@@ -145,10 +146,10 @@ path_kernel(const __grid_constant__ PathParams P) {
                                reinterpret_cast<unsigned char *>(s_exact),
                                reinterpret_cast<unsigned char *>(s_mat),
                                reinterpret_cast<unsigned char *>(s_aux)};
-      const uint32_t row[4] = {16u, 32u, 16u, 8u};
+      const uint32_t len[4] = {(npad + kGroup) * 16u, npad * 32u, npad * 16u, npad * 8u};
       for (int a = 0; a < 4; ++a)
-        for (uint32_t off = 0; off < npad * row[a]; off += kChunk)
-          bulk_g2s(dst[a] + off, src[a] + off, min(kChunk, npad * row[a] - off), &s_bar);
+        for (uint32_t off = 0; off < len[a]; off += kChunk)
+          bulk_g2s(dst[a] + off, src[a] + off, min(kChunk, len[a] - off), &s_bar);
     }
     mbar_wait(&s_bar, 0);
   }
@@ -241,7 +242,7 @@ path_kernel(const __grid_constant__ PathParams P) {
     // >= |o|^2 ; the row holds {c, r^2 - |c|^2 + slack} and the test is evaluated with slack on
     // both sides so that f32 rounding can only ADD candidates (filter error bound).
     float2 NOD[NP], OX2[NP], OY2[NP], OZ2[NP], OOT[NP];
-    uint32_t cnt[R];
+    uint32_t cnt = 0;  // 4 bits per slot: candidates in the slot's list
     uint32_t flushed = 0;  // bit r: slot r already has a running hit in s_hit_*
 #pragma unroll
     for (int p = 0; p < NP; ++p) {
@@ -256,7 +257,6 @@ path_kernel(const __grid_constant__ PathParams P) {
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      cnt[r] = 0;
       const bool live = depth[r] > 0;
       if (!live) PK(OOT, r) = __int_as_float(0x7f800000);  // idle slots never pass the filter
       nrays[r] += live ? 1.f : 0.f;
@@ -264,46 +264,62 @@ path_kernel(const __grid_constant__ PathParams P) {
 
     // Groups of kGroup rows: all FFMA2 chains of a group are independent (ILP hides the FMA
     // latency), the per-slot maximum over the group is compared once, and ONE branch per
-    // group leads to the rare path that re-examines the kept e values in sphere order.
-    for (uint32_t s0 = 0; s0 < npad; s0 += kGroup) {
-      float2 e[kGroup][NP];
+    // group leads to the rare path.  The next group's rows are fetched before the branch
+    // (software prefetch; the arrays carry one extra padding group), so the LDS latency is
+    // off the loop-carried path.
+    {
+      const float4 *frow = fast;
+      float4 S[kGroup];
 #pragma unroll
-      for (int k = 0; k < kGroup; ++k) {
-        const float4 S = fast[s0 + k];
-#pragma unroll
-        for (int p = 0; p < NP; ++p) {
-          float2 b = ffma2(bc(S.x), DX[p], ffma2(bc(S.y), DY[p], ffma2(bc(S.z), DZ[p], NOD[p])));
-          float2 q = ffma2(bc(S.x), OX2[p], ffma2(bc(S.y), OY2[p], ffma2(bc(S.z), OZ2[p], bc(S.w))));
-          e[k][p] = ffma2(b, b, q);
-        }
-      }
-      bool any = false;
-#pragma unroll
-      for (int p = 0; p < NP; ++p) {
-        float mx = e[0][p].x, my = e[0][p].y;
-#pragma unroll
-        for (int k = 1; k < kGroup; ++k) { mx = fmaxf(mx, e[k][p].x); my = fmaxf(my, e[k][p].y); }
-        any = any || mx >= OOT[p].x || my >= OOT[p].y;
-      }
-#if RTB_BRANCH_VOTE
-      if (__any_sync(0xffffffffu, any)) {
-#else
-      if (__builtin_expect(any, 0)) {
-#endif
+      for (int k = 0; k < kGroup; ++k) S[k] = frow[k];
+      for (uint32_t s0 = 0; s0 < npad; s0 += kGroup) {
+        float2 e[kGroup][NP];
 #pragma unroll
         for (int k = 0; k < kGroup; ++k) {
 #pragma unroll
-          for (int r = 0; r < R; ++r) {
-            if (PK(e[k], r) >= PK(OOT, r)) {
-              my_cand[(r * kCandCap + cnt[r]) * kBlock] = s0 + k;
-              if (++cnt[r] == kCandCap) {
-                flush_overflow(my_cand + r * kCandCap * kBlock, exact, PK(OX, r), PK(OY, r),
-                               PK(OZ, r), PK(DX, r), PK(DY, r), PK(DZ, r), dlen[r],
-                               s_hit_n + r * kBlock + tid, s_hit_id + r * kBlock + tid,
-                               !(flushed >> r & 1u));
-                flushed |= 1u << r;
-                cnt[r] = 0;
-              }
+          for (int p = 0; p < NP; ++p) {
+            float2 b = ffma2(bc(S[k].x), DX[p],
+                             ffma2(bc(S[k].y), DY[p], ffma2(bc(S[k].z), DZ[p], NOD[p])));
+            float2 q = ffma2(bc(S[k].x), OX2[p],
+                             ffma2(bc(S[k].y), OY2[p], ffma2(bc(S[k].z), OZ2[p], bc(S[k].w))));
+            e[k][p] = ffma2(b, b, q);
+          }
+        }
+        frow += kGroup;
+#pragma unroll
+        for (int k = 0; k < kGroup; ++k) S[k] = frow[k];
+        bool any = false;
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+          float mx = e[0][p].x, my = e[0][p].y;
+#pragma unroll
+          for (int k = 1; k < kGroup; ++k) { mx = fmaxf(mx, e[k][p].x); my = fmaxf(my, e[k][p].y); }
+          any = any || mx >= OOT[p].x || my >= OOT[p].y;
+        }
+        if (__builtin_expect(any, 0)) {
+          // bit (k*R + r): sphere s0+k survives for slot r; ascending bits = ascending sphere
+          // order within every slot
+          uint32_t m = 0;
+#pragma unroll
+          for (int k = 0; k < kGroup; ++k)
+#pragma unroll
+            for (int r = 0; r < R; ++r) m |= (PK(e[k], r) >= PK(OOT, r) ? 1u : 0u) << (k * R + r);
+          while (m) {
+            const uint32_t bit = (uint32_t)__ffs((int)m) - 1u;
+            m &= m - 1u;
+            const uint32_t r = bit % R, c = (cnt >> (4u * r)) & 15u;
+            my_cand[(r * kCandCap + c) * kBlock] = s0 + bit / R;
+            cnt += 1u << (4u * r);
+            if (c + 1u == kCandCap) {  // list full: resolve it now (rare)
+#pragma unroll
+              for (int rr = 0; rr < R; ++rr)
+                if (rr == (int)r)
+                  flush_overflow(my_cand + rr * kCandCap * kBlock, exact, PK(OX, rr), PK(OY, rr),
+                                 PK(OZ, rr), PK(DX, rr), PK(DY, rr), PK(DZ, rr), dlen[rr],
+                                 s_hit_n + rr * kBlock + tid, s_hit_id + rr * kBlock + tid,
+                                 !(flushed >> rr & 1u));
+              flushed |= 1u << r;
+              cnt &= ~(15u << (4u * r));
             }
           }
         }
@@ -320,7 +336,7 @@ path_kernel(const __grid_constant__ PathParams P) {
       double bestN = __longlong_as_double(0x7ff0000000000000ll);  // t_max = infinity
       int id = -1;
       if (flushed >> r & 1u) { bestN = s_hit_n[r * kBlock + tid]; id = s_hit_id[r * kBlock + tid]; }
-      resolve_list(my_cand + r * kCandCap * kBlock, cnt[r], exact, ray, bestN, id);
+      resolve_list(my_cand + r * kCandCap * kBlock, (cnt >> (4 * r)) & 15u, exact, ray, bestN, id);
       if (id < 0) {
         // sky, src/cpu/main.cc:27-29 (direction already unit length)
         float t = 0.5f * (dy + 1.0f);
@@ -425,7 +441,7 @@ cudaError_t launch_path(const PathParams &p, int rays_per_lane, int sm_count,
                         size_t smem_optin_max, cudaStream_t st, PathLaunchInfo *info) {
   int R = rays_per_lane ? rays_per_lane : 4;
   size_t lists = (size_t)kBlock * R * (kCandCap * 4 + 8 + 4);
-  size_t scene = (size_t)p.scene.n_pad * 72;
+  size_t scene = (size_t)p.scene.n_pad * 72 + kGroup * 16;
   bool in_smem = scene + lists + 1024 <= smem_optin_max;
   size_t smem = lists + (in_smem ? scene : 0);
 #define RTB_DISPATCH(RR)                                                               \
