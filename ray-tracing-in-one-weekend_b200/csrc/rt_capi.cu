@@ -73,9 +73,9 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
   *out = nullptr;
   if (n && !sp) return fail(RT_E_INVALID, "spheres is NULL");
   if (n > (1u << 24)) return fail(RT_E_INVALID, "too many spheres (%u)", n);
-  // rows are padded to a multiple of 4 (the filter loop is unrolled by 4); a padding row has
+  // rows are padded to a multiple of 8 (the filter loop takes two groups of 4 per trip); a padding row has
   // w = -inf so that b*b + q = -inf never reaches the threshold
-  const uint32_t npad = n ? (n + 3u) & ~3u : 4u;
+  const uint32_t npad = n ? (n + 7u) & ~7u : 8u;
   std::vector<float4> fast(npad + 4, make_float4(0.f, 0.f, 0.f, -INFINITY));  // + prefetch group
   std::vector<double4> exact(npad, make_double4(0, 0, 0, 1));
   std::vector<float4> mat(npad, make_float4(0.f, 0.f, 0.f, 0.f));

@@ -15,7 +15,7 @@ struct SceneView {
   const float4 *mat;     // [n] {albedo.r, albedo.g, albedo.b, fuzz | ir}
   const float2 *aux;     // [n] {1 / signed radius, material kind (integer bits)}
   uint32_t n;            // spheres in the hittable_list
-  uint32_t n_pad;        // rows allocated: n rounded up to a multiple of 4; padding rows can
+  uint32_t n_pad;        // rows allocated: n rounded up to a multiple of 8; padding rows can
                          // never pass the filter (w = -inf)
 };
 

@@ -27,7 +27,13 @@ namespace rtb {
 #define RTB_BRANCH_VOTE 0  // 1: warp-uniform vote + branch; 0: plain divergent branch
 #endif
 
-constexpr int kBlock = 256;
+#ifndef RTB_BLOCK
+#define RTB_BLOCK 256
+#endif
+#ifndef RTB_MINB2
+#define RTB_MINB2 2  // resident CTAs per SM the R = 2 kernel is compiled for
+#endif
+constexpr int kBlock = RTB_BLOCK;
 constexpr int kCandCap = 8;  // candidate list capacity per slot before an in-loop flush
 constexpr int kGroup = 4;    // sphere rows per filter group (scene rows are padded to this)
 
@@ -49,6 +55,18 @@ __device__ __forceinline__ float2 bc(float v) { return make_float2(v, v); }  // 
 // all spheres of a ray, so roots are compared as N against t_min*a and bestN (no division).
 // Inclusive upper bound: a later sphere with an equal root replaces the earlier one
 // (hittable_list.h:34-39 + sphere.h:38-40).
+// sqrt of a non-negative double: f32 reciprocal-square-root seed + two Heron steps in f64
+// (relative error ~2^-45 after the first, below 1 ulp after the second); no IEEE fix-up code.
+__device__ __forceinline__ double fast_dsqrt(double x) {
+  float xf = fmaxf((float)x, 1e-30f);
+  double y = (double)rsqrtf(xf);   // ~ 1/sqrt(x), rel. error 2^-22
+  double h = 0.5 * y;
+  double s = x * y;
+  s = fma(fma(-s, s, x), h, s);
+  s = fma(fma(-s, s, x), h, s);
+  return s;
+}
+
 struct RayD {
   double ox, oy, oz, dx, dy, dz, a, tminA;
 };
@@ -59,7 +77,7 @@ __device__ __forceinline__ bool exact_hit_num(const double4 S, const RayD &r, do
   double c = ocx * ocx + ocy * ocy + ocz * ocz - S.w * S.w;
   double disc = half_b * half_b - r.a * c;
   if (disc < 0.0) return false;
-  double sq = sqrt(disc);
+  double sq = fast_dsqrt(disc);
   double N = -half_b - sq;
   if (N < r.tminA || bestN < N) {
     N = -half_b + sq;
@@ -103,7 +121,7 @@ __device__ __noinline__ void flush_overflow(const uint32_t *list, const double4 
 // ---------------------------------------------------------------- the kernel
 // R = slots (rays in flight) per lane, even; SMEM = scene rows live in shared memory.
 template <int R, bool SMEM>
-__global__ void __launch_bounds__(kBlock, (R <= 2 ? 2 : 1))
+__global__ void __launch_bounds__(kBlock, (R <= 2 ? RTB_MINB2 : 1))
 path_kernel(const __grid_constant__ PathParams P) {
   static_assert(R % 2 == 0, "slots are packed in pairs");
   constexpr int NP = R / 2;
@@ -272,7 +290,10 @@ path_kernel(const __grid_constant__ PathParams P) {
       float4 S[kGroup];
 #pragma unroll
       for (int k = 0; k < kGroup; ++k) S[k] = frow[k];
-      for (uint32_t s0 = 0; s0 < npad; s0 += kGroup) {
+      uint32_t npad_r = npad;
+      asm volatile("" : "+r"(npad_r));  // keep the bound in a register (no per-iteration LDCU)
+#pragma unroll 2
+      for (uint32_t s0 = 0; s0 < npad_r; s0 += kGroup) {
         float2 e[kGroup][NP];
 #pragma unroll
         for (int k = 0; k < kGroup; ++k) {
@@ -349,7 +370,8 @@ path_kernel(const __grid_constant__ PathParams P) {
       }
       // hit record, src/cpu/sphere.h:43-48 + hittable.h:16-19: point in f64, then narrowed
       const double4 S = exact[id];
-      const double t = bestN / ray.a;
+      // t = bestN / a with a = 1 + eps (|eps| ~ 1e-7): 1/a = 2 - a to within eps^2
+      const double t = bestN * (2.0 - ray.a);
       const double px = ray.ox + t * ray.dx, py = ray.oy + t * ray.dy, pz = ray.oz + t * ray.dz;
       const float2 ax = aux[id];  // {1/r (signed), kind}
       float onx = (float)(px - S.x) * ax.x, ony = (float)(py - S.y) * ax.x,
