@@ -40,6 +40,7 @@ struct rt_scene {
   float4 *mat;
   float2 *aux;
   uint32_t n_pad;
+  std::vector<float4> host_fast;  // host copy of the filter rows (kernel-parameter path)
 };
 
 struct rt_frame {
@@ -126,6 +127,7 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
   CU(cudaMemcpy(sc->exact, exact.data(), m * sizeof(double4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->mat, mat.data(), m * sizeof(float4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->aux, aux.data(), m * sizeof(float2), cudaMemcpyHostToDevice));
+  sc->host_fast = fast;
   *out = sc;
   return RT_OK;
 }
@@ -306,7 +308,7 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
     int rpl = 0;
     if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
     PathLaunchInfo info;
-    CU(launch_path(p, rpl, f->sm_count, f->smem_optin, f->stream, &info));
+    CU(launch_path(p, sc->host_fast.data(), rpl, f->sm_count, f->smem_optin, f->stream, &info));
     launches = 1;
   }
   CU(cudaEventRecord(f->ev[1], f->stream));

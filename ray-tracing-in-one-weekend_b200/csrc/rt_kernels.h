@@ -25,12 +25,21 @@ struct PathParams {
 struct PathLaunchInfo {
   int rays_per_lane, grid, block, blocks_per_sm;
   size_t smem_bytes;
-  bool scene_in_smem;
+  bool scene_in_smem, rows_in_constant_bank;
+};
+
+// Filter rows passed by value as a kernel parameter (constant bank 0): scenes of up to
+// kConstRows - 4 padded rows.  16 KB of the 32 KB parameter space.
+constexpr int kConstRows = 1024;
+struct ConstRows {
+  float4 row[kConstRows];
 };
 
 // rays_per_lane: 1, 2 or 4 (0 = default).  Launches the persistent path kernel.
-cudaError_t launch_path(const PathParams &p, int rays_per_lane, int sm_count,
-                        size_t smem_optin_max, cudaStream_t st, PathLaunchInfo *info);
+// host_rows: host copy of scene.fast (n_pad + 4 rows) or nullptr.
+cudaError_t launch_path(const PathParams &p, const float4 *host_rows, int rays_per_lane,
+                        int sm_count, size_t smem_optin_max, cudaStream_t st,
+                        PathLaunchInfo *info);
 
 // dst[i] = canonical sub-tree sum of slices [slice_begin, slice_end) (aligned power of 2).
 cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t slice_begin,

@@ -21,6 +21,9 @@
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
+#include <cstdlib>
+#include <cstring>
+
 namespace rtb {
 
 #ifndef RTB_BRANCH_VOTE
@@ -120,9 +123,13 @@ __device__ __noinline__ void flush_overflow(const uint32_t *list, const double4 
 
 // ---------------------------------------------------------------- the kernel
 // R = slots (rays in flight) per lane, even; SMEM = scene rows live in shared memory.
-template <int R, bool SMEM>
+// CROWS = filter rows are read from the kernel-parameter (constant) bank through uniform
+// registers (LDCU): every FFMA2 of the filter then has exactly one sphere operand, a uniform
+// register, and reads at most two register pairs -> the register file is no longer the limit
+// (tools/microbench.cu, "FFMA2 uniform-register multiplier").
+template <int R, bool SMEM, bool CROWS>
 __global__ void __launch_bounds__(kBlock, (R <= 2 ? RTB_MINB2 : 1))
-path_kernel(const __grid_constant__ PathParams P) {
+path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstRows CR) {
   static_assert(R % 2 == 0, "slots are packed in pairs");
   constexpr int NP = R / 2;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -252,7 +259,7 @@ path_kernel(const __grid_constant__ PathParams P) {
       }
       all_dead = all_dead && depth[r] < 0;
     }
-    if (all_dead) break;
+    if (__all_sync(0xffffffffu, all_dead)) break;  // warp-uniform exit keeps the loop convergent
 
     // ------------------------------------------------------------ (2) filter: all spheres
     // hittable_list::hit (src/cpu/hittable_list.h:28-43) visits every sphere in order.  The
@@ -285,11 +292,17 @@ path_kernel(const __grid_constant__ PathParams P) {
     // group leads to the rare path.  The next group's rows are fetched before the branch
     // (software prefetch; the arrays carry one extra padding group), so the LDS latency is
     // off the loop-carried path.
+#ifdef RTB_LOOP_REPEAT  // timing experiment only: run the filter pass several times
+    for (int rep = 0; rep < RTB_LOOP_REPEAT; ++rep)
+#endif
     {
+#ifdef RTB_LOOP_REPEAT
+      cnt = 0; flushed = 0;
+#endif
       const float4 *frow = fast;
       float4 S[kGroup];
 #pragma unroll
-      for (int k = 0; k < kGroup; ++k) S[k] = frow[k];
+      for (int k = 0; k < kGroup; ++k) S[k] = CROWS ? CR.row[k] : frow[k];
       uint32_t npad_r = npad;
       asm volatile("" : "+r"(npad_r));  // keep the bound in a register (no per-iteration LDCU)
 #pragma unroll 2
@@ -299,16 +312,18 @@ path_kernel(const __grid_constant__ PathParams P) {
         for (int k = 0; k < kGroup; ++k) {
 #pragma unroll
           for (int p = 0; p < NP; ++p) {
+            // e = (c.d - o.d)^2 + (2 c.o + w), as one chain in which every FFMA2 multiplies
+            // by exactly one sphere scalar
             float2 b = ffma2(bc(S[k].x), DX[p],
                              ffma2(bc(S[k].y), DY[p], ffma2(bc(S[k].z), DZ[p], NOD[p])));
-            float2 q = ffma2(bc(S[k].x), OX2[p],
-                             ffma2(bc(S[k].y), OY2[p], ffma2(bc(S[k].z), OZ2[p], bc(S[k].w))));
-            e[k][p] = ffma2(b, b, q);
+            float2 e1 = ffma2(b, b, bc(S[k].w));
+            e[k][p] = ffma2(bc(S[k].x), OX2[p],
+                            ffma2(bc(S[k].y), OY2[p], ffma2(bc(S[k].z), OZ2[p], e1)));
           }
         }
         frow += kGroup;
 #pragma unroll
-        for (int k = 0; k < kGroup; ++k) S[k] = frow[k];
+        for (int k = 0; k < kGroup; ++k) S[k] = CROWS ? CR.row[s0 + kGroup + k] : frow[k];
         bool any = false;
 #pragma unroll
         for (int p = 0; p < NP; ++p) {
@@ -317,7 +332,7 @@ path_kernel(const __grid_constant__ PathParams P) {
           for (int k = 1; k < kGroup; ++k) { mx = fmaxf(mx, e[k][p].x); my = fmaxf(my, e[k][p].y); }
           any = any || mx >= OOT[p].x || my >= OOT[p].y;
         }
-        if (__builtin_expect(any, 0)) {
+        if (CROWS ? __any_sync(0xffffffffu, any) : __builtin_expect(any, 0)) {
           // bit (k*R + r): sphere s0+k survives for slot r; ascending bits = ascending sphere
           // order within every slot
           uint32_t m = 0;
@@ -439,10 +454,10 @@ path_kernel(const __grid_constant__ PathParams P) {
 }
 
 // ---------------------------------------------------------------- launcher
-template <int R, bool SMEM>
-static cudaError_t launch_path_t(const PathParams &p, int sm_count, size_t smem, cudaStream_t st,
-                                 PathLaunchInfo *info) {
-  auto kern = path_kernel<R, SMEM>;
+template <int R, bool SMEM, bool CROWS>
+static cudaError_t launch_path_t(const PathParams &p, const ConstRows &cr, int sm_count,
+                                 size_t smem, cudaStream_t st, PathLaunchInfo *info) {
+  auto kern = path_kernel<R, SMEM, CROWS>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0;
@@ -454,21 +469,28 @@ static cudaError_t launch_path_t(const PathParams &p, int sm_count, size_t smem,
   if (info) {
     info->rays_per_lane = R; info->grid = grid; info->block = kBlock;
     info->blocks_per_sm = per_sm; info->smem_bytes = smem; info->scene_in_smem = SMEM;
+    info->rows_in_constant_bank = CROWS;
   }
-  kern<<<grid, kBlock, smem, st>>>(p);
+  kern<<<grid, kBlock, smem, st>>>(p, cr);
   return cudaGetLastError();
 }
 
-cudaError_t launch_path(const PathParams &p, int rays_per_lane, int sm_count,
-                        size_t smem_optin_max, cudaStream_t st, PathLaunchInfo *info) {
-  int R = rays_per_lane ? rays_per_lane : 4;
+cudaError_t launch_path(const PathParams &p, const float4 *host_rows, int rays_per_lane,
+                        int sm_count, size_t smem_optin_max, cudaStream_t st,
+                        PathLaunchInfo *info) {
+  int R = rays_per_lane ? rays_per_lane : 2;
   size_t lists = (size_t)kBlock * R * (kCandCap * 4 + 8 + 4);
   size_t scene = (size_t)p.scene.n_pad * 72 + kGroup * 16;
   bool in_smem = scene + lists + 1024 <= smem_optin_max;
   size_t smem = lists + (in_smem ? scene : 0);
-#define RTB_DISPATCH(RR)                                                               \
-  return in_smem ? launch_path_t<RR, true>(p, sm_count, smem, st, info)                \
-                 : launch_path_t<RR, false>(p, sm_count, smem, st, info)
+  static ConstRows cr;  // rows beyond the scene are never read
+  bool crows = in_smem && host_rows && p.scene.n_pad + kGroup <= (uint32_t)kConstRows &&
+               !getenv("RT_B200_NO_CONST_ROWS");
+  if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kGroup) * sizeof(float4));
+#define RTB_DISPATCH(RR)                                                                  \
+  return crows     ? launch_path_t<RR, true, true>(p, cr, sm_count, smem, st, info)       \
+         : in_smem ? launch_path_t<RR, true, false>(p, cr, sm_count, smem, st, info)      \
+                   : launch_path_t<RR, false, false>(p, cr, sm_count, smem, st, info)
   switch (R) {
     case 2: RTB_DISPATCH(2);
     case 4: RTB_DISPATCH(4);
