@@ -76,8 +76,8 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
   if (n > (1u << 24)) return fail(RT_E_INVALID, "too many spheres (%u)", n);
   // rows are padded to a multiple of 8 (the filter loop takes two groups of 4 per trip); a padding row has
   // w = -inf so that b*b + q = -inf never reaches the threshold
-  const uint32_t npad = n ? (n + 7u) & ~7u : 8u;
-  std::vector<float4> fast(npad + 4, make_float4(0.f, 0.f, 0.f, -INFINITY));  // + prefetch group
+  const uint32_t npad = n ? (n + kRowPad - 1) / kRowPad * kRowPad : kRowPad;
+  std::vector<float4> fast(npad + kRowTail, make_float4(0.f, 0.f, 0.f, -INFINITY));  // + prefetch group
   std::vector<double4> exact(npad, make_double4(0, 0, 0, 1));
   std::vector<float4> mat(npad, make_float4(0.f, 0.f, 0.f, 0.f));
   std::vector<float2> aux(npad, make_float2(1.f, 0.f));
@@ -116,14 +116,14 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
   sc->device = device; sc->n = n; sc->n_pad = npad;
   size_t m = npad;
   cudaError_t e;
-  if ((e = cudaMalloc(&sc->fast, (m + 4) * sizeof(float4))) != cudaSuccess ||
+  if ((e = cudaMalloc(&sc->fast, (m + kRowTail) * sizeof(float4))) != cudaSuccess ||
       (e = cudaMalloc(&sc->exact, m * sizeof(double4))) != cudaSuccess ||
       (e = cudaMalloc(&sc->mat, m * sizeof(float4))) != cudaSuccess ||
       (e = cudaMalloc(&sc->aux, m * sizeof(float2))) != cudaSuccess) {
     rt_scene_destroy(sc);
     return fail(RT_E_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
   }
-  CU(cudaMemcpy(sc->fast, fast.data(), (m + 4) * sizeof(float4), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(sc->fast, fast.data(), (m + kRowTail) * sizeof(float4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->exact, exact.data(), m * sizeof(double4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->mat, mat.data(), m * sizeof(float4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->aux, aux.data(), m * sizeof(float2), cudaMemcpyHostToDevice));

@@ -10,12 +10,12 @@ namespace rtb {
 // ---------------------------------------------------------------- flattened scene (HBM)
 // hittable_list (src/cpu/hittable_list.h:12-26) flattened in insertion order.
 struct SceneView {
-  const float4 *fast;    // [n_pad + 4] {cx, cy, cz, r^2-|c|^2 + slack}  conservative f32 filter row
+  const float4 *fast;    // [n_pad + kRowTail] {cx, cy, cz, r^2-|c|^2 + slack}  conservative f32 filter row
   const double4 *exact;  // [n_pad] {cx, cy, cz, signed radius}       f64 candidate resolution
   const float4 *mat;     // [n] {albedo.r, albedo.g, albedo.b, fuzz | ir}
   const float2 *aux;     // [n] {1 / signed radius, material kind (integer bits)}
   uint32_t n;            // spheres in the hittable_list
-  uint32_t n_pad;        // rows allocated: n rounded up to a multiple of 8; padding rows can
+  uint32_t n_pad;        // rows allocated: n rounded up to a multiple of kRowPad; padding rows can
                          // never pass the filter (w = -inf)
 };
 

@@ -8,6 +8,10 @@
 
 #define RT_SLICES_DEV 8u
 
+// Scene rows are padded to a multiple of kRowPad (padding rows never pass the filter) and the
+// filter-row array carries kRowTail more padding rows for the loop's prefetch.
+constexpr unsigned kRowPad = 8, kRowTail = 8;
+
 namespace rtb {
 
 struct PathParams {

@@ -38,7 +38,11 @@ namespace rtb {
 #endif
 constexpr int kBlock = RTB_BLOCK;
 constexpr int kCandCap = 8;  // candidate list capacity per slot before an in-loop flush
-constexpr int kGroup = 4;    // sphere rows per filter group (scene rows are padded to this)
+#ifndef RTB_GROUP
+#define RTB_GROUP 4
+#endif
+constexpr int kGroup = RTB_GROUP;  // sphere rows per filter group; kRowPad is a multiple of 2*kGroup
+static_assert(kRowPad % (2 * kGroup) == 0 && kRowTail >= kGroup, "row padding");
 
 // ---------------------------------------------------------------- packed f32x2 helpers
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
@@ -137,8 +141,8 @@ path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstR
   const uint32_t tid = threadIdx.x;
 
   // ---- shared memory carve-up (scene part only when SMEM)
-  const size_t scene_bytes = SMEM ? (size_t)npad * 72 + kGroup * 16 : 0;
-  // [exact npad*32][mat npad*16][aux npad*8][fast (npad + kGroup)*16]
+  const size_t scene_bytes = SMEM ? (size_t)npad * 72 + kRowTail * 16 : 0;
+  // [exact npad*32][mat npad*16][aux npad*8][fast (npad + kRowTail)*16]
   double4 *s_exact = reinterpret_cast<double4 *>(smem_raw);
   float4 *s_mat = reinterpret_cast<float4 *>(smem_raw + (size_t)npad * 32);
   float2 *s_aux = reinterpret_cast<float2 *>(smem_raw + (size_t)npad * 48);
@@ -161,7 +165,7 @@ path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstR
     if (tid == 0) mbar_init(&s_bar, 1);
     __syncthreads();
     if (tid == 0) {
-      mbar_expect_tx(&s_bar, npad * 72u + kGroup * 16u);
+      mbar_expect_tx(&s_bar, npad * 72u + kRowTail * 16u);
       const uint32_t kChunk = 32768u;
       const unsigned char *src[4] = {reinterpret_cast<const unsigned char *>(P.scene.fast),
                                      reinterpret_cast<const unsigned char *>(P.scene.exact),
@@ -171,7 +175,7 @@ path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstR
                                reinterpret_cast<unsigned char *>(s_exact),
                                reinterpret_cast<unsigned char *>(s_mat),
                                reinterpret_cast<unsigned char *>(s_aux)};
-      const uint32_t len[4] = {(npad + kGroup) * 16u, npad * 32u, npad * 16u, npad * 8u};
+      const uint32_t len[4] = {(npad + kRowTail) * 16u, npad * 32u, npad * 16u, npad * 8u};
       for (int a = 0; a < 4; ++a)
         for (uint32_t off = 0; off < len[a]; off += kChunk)
           bulk_g2s(dst[a] + off, src[a] + off, min(kChunk, len[a] - off), &s_bar);
@@ -480,13 +484,13 @@ cudaError_t launch_path(const PathParams &p, const float4 *host_rows, int rays_p
                         PathLaunchInfo *info) {
   int R = rays_per_lane ? rays_per_lane : 2;
   size_t lists = (size_t)kBlock * R * (kCandCap * 4 + 8 + 4);
-  size_t scene = (size_t)p.scene.n_pad * 72 + kGroup * 16;
+  size_t scene = (size_t)p.scene.n_pad * 72 + kRowTail * 16;
   bool in_smem = scene + lists + 1024 <= smem_optin_max;
   size_t smem = lists + (in_smem ? scene : 0);
   static ConstRows cr;  // rows beyond the scene are never read
-  bool crows = in_smem && host_rows && p.scene.n_pad + kGroup <= (uint32_t)kConstRows &&
+  bool crows = in_smem && host_rows && p.scene.n_pad + kRowTail <= (uint32_t)kConstRows &&
                !getenv("RT_B200_NO_CONST_ROWS");
-  if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kGroup) * sizeof(float4));
+  if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
 #define RTB_DISPATCH(RR)                                                                  \
   return crows     ? launch_path_t<RR, true, true>(p, cr, sm_count, smem, st, info)       \
          : in_smem ? launch_path_t<RR, true, false>(p, cr, sm_count, smem, st, info)      \

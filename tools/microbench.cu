@@ -86,74 +86,74 @@ void run(const char *name, int sms, int blocks_per_sm) {
 }
 
 
-// ---- sphere-row feed variants: one {x,y,z,w} row per NP*7 FFMA2, rows from shared memory
-// (broadcast LDS.128) or from the constant bank through uniform registers (LDCU).
+// ---- filter-loop replicas: the path kernel's filter without the rare path.  NP slot pairs,
+// G rows per group; rows from shared memory (broadcast LDS.128 -> .F32 register operands) or
+// from the constant bank through uniform registers (LDCU -> .F32 uniform operands).
 __device__ __forceinline__ float2 bc(float v) { return make_float2(v, v); }
-__constant__ float4 c_rows[512];
-__constant__ float c_w[512];
+struct Rows { float4 row[520]; };
 
-template <int NP, bool CONSTANT>
-__global__ void __launch_bounds__(256) feed(float *out, int iters, const float4 *g_rows, float thr) {
-  __shared__ float4 s_rows[512];
-  for (int k = threadIdx.x; k < 512; k += 256) s_rows[k] = g_rows[k];
+template <int NP, int G, bool CONSTANT>
+__global__ void __launch_bounds__(256) feed(float *out, int iters, const float4 *g_rows, float thr,
+                                            const __grid_constant__ Rows CR) {
+  __shared__ float4 s_rows[520];
+  for (int k = threadIdx.x; k < 520; k += 256) s_rows[k] = g_rows[k];
   __syncthreads();
   float2 D0[NP], D1[NP], D2[NP], N0[NP], O0[NP], O1[NP], O2[NP];
 #pragma unroll
   for (int p = 0; p < NP; ++p) {
-    float t = (float)(threadIdx.x + p) * 1e-3f;
-    D0[p] = make_float2(t, t + 1); D1[p] = make_float2(t + 2, t + 3); D2[p] = make_float2(t + 4, t + 5);
-    N0[p] = make_float2(t, -t); O0[p] = make_float2(t * 2, t * 3); O1[p] = make_float2(t * 4, t * 5);
-    O2[p] = make_float2(t * 6, t * 7);
+    const float *g = reinterpret_cast<const float *>(g_rows) + threadIdx.x + 16 * p;
+    D0[p] = make_float2(g[0], g[1]); D1[p] = make_float2(g[2], g[3]); D2[p] = make_float2(g[4], g[5]);
+    N0[p] = make_float2(g[6], g[7]); O0[p] = make_float2(g[8], g[9]); O1[p] = make_float2(g[10], g[11]);
+    O2[p] = make_float2(g[12], g[13]);
   }
-  int cnt = 0;
+  float sink = 0.f;
   for (int i = 0; i < iters; ++i) {
-#pragma unroll 4
-    for (int s = 0; s < 512; ++s) {
-      float4 S = CONSTANT ? c_rows[s] : s_rows[s];
-      bool any = false;
-      if (CONSTANT) {  // x,y,z stay in uniform registers; w comes from its own array into a vector register
-        S.w = c_w[s];
-        asm volatile("" : "+f"(S.w));
-      }
+#pragma unroll 2
+    for (int s0 = 0; s0 < 512; s0 += G) {
+      float mx[NP], my[NP];
 #pragma unroll
-      for (int p = 0; p < NP; ++p) {
-        float2 b = ffma2(bc(S.x), D0[p], ffma2(bc(S.y), D1[p], ffma2(bc(S.z), D2[p], N0[p])));
-        float2 q = ffma2(bc(S.x), O0[p], ffma2(bc(S.y), O1[p], ffma2(bc(S.z), O2[p], bc(S.w))));
-        float2 e = ffma2(b, b, q);
-        any = any || e.x >= thr || e.y >= thr;
+      for (int k = 0; k < G; ++k) {
+        float4 S = CONSTANT ? CR.row[s0 + k] : s_rows[s0 + k];
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+          float2 b = ffma2(bc(S.x), D0[p], ffma2(bc(S.y), D1[p], ffma2(bc(S.z), D2[p], N0[p])));
+          float2 e1 = ffma2(b, b, bc(S.w));
+          float2 e = ffma2(bc(S.x), O0[p], ffma2(bc(S.y), O1[p], ffma2(bc(S.z), O2[p], e1)));
+          mx[p] = k ? fmaxf(mx[p], e.x) : e.x;
+          my[p] = k ? fmaxf(my[p], e.y) : e.y;
+        }
       }
-      if (any) cnt += s;
+      bool any = false;
+#pragma unroll
+      for (int p = 0; p < NP; ++p) any = any || mx[p] >= thr || my[p] >= thr;
+      if (__any_sync(0xffffffffu, any)) sink += 1.f;
     }
   }
-  out[blockIdx.x * blockDim.x + threadIdx.x] = (float)cnt;
+  out[blockIdx.x * blockDim.x + threadIdx.x] = sink;
 }
 
-template <int NP, bool CONSTANT>
+template <int NP, int G, bool CONSTANT>
 void run_feed(const char *name, int sms, int blocks_per_sm) {
-  int blocks = sms * blocks_per_sm, iters = 40;
+  int blocks = sms * blocks_per_sm, iters = 200;
   float *out; float4 *rows;
   CK(cudaMalloc(&out, (size_t)blocks * 256 * 4));
-  CK(cudaMalloc(&rows, 512 * 16));
-  float4 h[512];
-  for (int k = 0; k < 512; ++k) h[k] = make_float4(k * 1e-3f, 1.f - k * 1e-3f, 0.5f, -1e30f);
-  CK(cudaMemcpy(rows, h, sizeof h, cudaMemcpyHostToDevice));
-  CK(cudaMemcpyToSymbol(c_rows, h, sizeof h));
-  float hw[512];
-  for (int k = 0; k < 512; ++k) hw[k] = h[k].w;
-  CK(cudaMemcpyToSymbol(c_w, hw, sizeof hw));
+  CK(cudaMalloc(&rows, 520 * 16));
+  static Rows h;
+  for (int k = 0; k < 520; ++k) h.row[k] = make_float4(k * 1e-3f, 1.f - k * 1e-3f, 0.5f + k * 1e-4f, -1e3f - k);
+  CK(cudaMemcpy(rows, h.row, sizeof h, cudaMemcpyHostToDevice));
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   float best = 1e30f;
   for (int rep = 0; rep < 4; ++rep) {
     CK(cudaEventRecord(e0));
-    feed<NP, CONSTANT><<<blocks, 256>>>(out, iters, rows, 1e30f);
+    feed<NP, G, CONSTANT><<<blocks, 256>>>(out, iters, rows, 1e30f, h);
     CK(cudaEventRecord(e1));
     CK(cudaEventSynchronize(e1));
     float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
     if (rep && ms < best) best = ms;
   }
   double fma = 14.0 * NP * 512.0 * iters * 256.0 * blocks;
-  printf("%-34s %2d blk/SM  %7.2f TFLOP/s  (%.3f ms)\n", name, blocks_per_sm, 2.0 * fma / (best * 1e-3) / 1e12, best);
+  printf("%-40s %2d blk/SM  %7.2f TFLOP/s  (%.3f ms)\n", name, blocks_per_sm, 2.0 * fma / (best * 1e-3) / 1e12, best);
   cudaFree(out); cudaFree(rows);
 }
 
@@ -232,10 +232,12 @@ int main() {
     run_rf<3>("FFMA2 uniform-register multiplier (.F32 UR)", sms, bps);
   }
   for (int bps : {2, 4}) {
-    run_feed<1, false>("filter R=2 rows via LDS.128", sms, bps);
-    run_feed<1, true>("filter R=2 rows via LDCU", sms, bps);
-    run_feed<2, false>("filter R=4 rows via LDS.128", sms, bps);
-    run_feed<2, true>("filter R=4 rows via LDCU", sms, bps);
+    run_feed<1, 4, false>("filter R=2 G=4 rows via LDS.128", sms, bps);
+    run_feed<1, 4, true>("filter R=2 G=4 rows via LDCU", sms, bps);
+    run_feed<1, 8, true>("filter R=2 G=8 rows via LDCU", sms, bps);
+    run_feed<2, 4, false>("filter R=4 G=4 rows via LDS.128", sms, bps);
+    run_feed<2, 4, true>("filter R=4 G=4 rows via LDCU", sms, bps);
+    run_feed<2, 2, true>("filter R=4 G=2 rows via LDCU", sms, bps);
   }
   return 0;
 }
