@@ -65,6 +65,8 @@ typedef struct rt_config {
 } rt_config;
 
 #define RT_FLAG_COUNT_RAYS 1u /* fill rt_stats.rays (one atomic per work item) */
+#define RT_FLAG_MEGAKERNEL 2u /* register-resident megakernel (rt_path.cu) instead of the fused kernel */
+#define RT_FLAG_WAVEFRONT 4u  /* two-kernel shade/filter wavefront (rt_wave.cu) */
 
 typedef struct rt_stats {
   uint64_t samples;      /* samples traced by this call */

@@ -57,6 +57,10 @@ struct rt_frame {
   int sm_count;
   size_t smem_optin;
   uint32_t last_n;
+  void *pool;               // wavefront path-slot pool (allocated on first use)
+  uint32_t pool_slots;
+  unsigned int *live;       // device counter
+  unsigned int *host_live;  // pinned
 };
 
 extern "C" const char *rt_last_error(void) { return g_err; }
@@ -241,6 +245,8 @@ extern "C" int rt_frame_destroy(rt_frame *f) {
   cudaSetDevice(f->device);
   cudaFree(f->accum); cudaFree(f->partial); cudaFree(f->rgb_words); cudaFree(f->linear);
   cudaFree(f->counters);
+  cudaFree(f->pool); cudaFree(f->live);
+  if (f->host_live) cudaFreeHost(f->host_live);
   for (int k = 0; k < 4; ++k)
     if (f->ev[k]) cudaEventDestroy(f->ev[k]);
   if (f->own_stream) cudaStreamDestroy(f->own_stream);
@@ -277,6 +283,13 @@ static int check_cfg(const rt_config *cfg, const rt_frame *f) {
 }
 
 // ---------------------------------------------------------------- the hot path
+// 0 = fused persistent kernel (default), 1 = register-resident megakernel, 2 = two-kernel wavefront
+static int render_mode(const rt_config *cfg) {
+  if (const char *e = getenv("RT_B200_MODE"))
+    return strcmp(e, "mega") == 0 ? 1 : strcmp(e, "wave") == 0 ? 2 : 0;
+  return (cfg->flags & RT_FLAG_MEGAKERNEL) ? 1 : (cfg->flags & RT_FLAG_WAVEFRONT) ? 2 : 0;
+}
+
 extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_config *cfg,
                          rt_frame *f, rt_stats *stats) {
   if (!sc || !cam) return fail(RT_E_INVALID, "NULL argument");
@@ -304,12 +317,37 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
     CU(cudaMemsetAsync(f->accum + (size_t)cfg->slice_begin * f->npix, 0,
                        (size_t)(cfg->slice_end - cfg->slice_begin) * f->npix * sizeof(float4),
                        f->stream));
-  } else {
+  } else if (render_mode(cfg) == 1) {
     int rpl = 0;
     if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
     PathLaunchInfo info;
     CU(launch_path(p, sc->host_fast.data(), rpl, f->sm_count, f->smem_optin, f->stream, &info));
     launches = 1;
+  } else {
+    // wavefront: shade / filter kernels alternating over a pool of path slots
+    if (!f->pool) {
+      uint32_t slots = wave_default_slots(f->sm_count);
+      if (const char *e = getenv("RT_B200_WAVE_SLOTS")) slots = (uint32_t)atol(e) / 1024u * 1024u;
+      if (slots < 1024u) return fail(RT_E_INVALID, "RT_B200_WAVE_SLOTS too small");
+      CU(cudaMalloc(&f->pool, wave_pool_bytes(slots)));
+      CU(cudaMalloc(&f->live, sizeof(unsigned int)));
+      CU(cudaMallocHost(&f->host_live, sizeof(unsigned int)));
+      f->pool_slots = slots;
+    }
+    WaveParams w;
+    w.scene = p.scene; w.cam = p.cam; w.width = p.width; w.height = p.height;
+    w.spp = p.spp; w.max_depth = p.max_depth; w.seed = p.seed; w.sample_offset = p.sample_offset;
+    w.slice_begin = p.slice_begin; w.slice_end = p.slice_end;
+    w.accum = p.accum; w.counter = p.counter; w.live = f->live;
+    WaveRunInfo info;
+    if (render_mode(cfg) == 2) {
+      wave_carve(w, f->pool, f->pool_slots);
+      CU(run_wavefront(w, sc->host_fast.data(), f->sm_count, f->smem_optin, f->stream, f->host_live, &info));
+    } else {
+      CU(run_fused(w, f->pool, f->pool_slots, sc->host_fast.data(), f->sm_count, f->smem_optin,
+                   f->stream, &info));
+    }
+    launches = info.launches;
   }
   CU(cudaEventRecord(f->ev[1], f->stream));
   CU(cudaStreamSynchronize(f->stream));

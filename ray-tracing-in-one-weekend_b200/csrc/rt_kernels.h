@@ -39,6 +39,50 @@ struct ConstRows {
   float4 row[kConstRows];
 };
 
+// ---------------------------------------------------------------- wavefront form (rt_wave.cu)
+constexpr unsigned kCandPlanes = 16;  // candidate indices kept per ray before the exact full scan
+
+struct WaveParams {
+  SceneView scene;
+  CameraF32 cam;
+  uint32_t width, height;
+  uint32_t spp, max_depth;
+  uint64_t seed;
+  uint32_t sample_offset;
+  uint32_t slice_begin, slice_end;
+  float4 *accum;                // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
+  unsigned long long *counter;  // work-queue head (zeroed before the frame)
+  unsigned int *live;           // rays produced by the last polled shade pass
+  // pool of path slots (SoA, n_slots each)
+  uint32_t n_slots;
+  float4 *ray_o;       // {ox, oy, oz, |d| of the reference's un-normalised ray; < 0 = no ray}
+  float4 *ray_d;       // {unit direction, -}
+  float4 *thr;         // {throughput r, g, b, depth (int bits): >0 bounces left, 0 new path, -1 retired}
+  float4 *acc;         // {item sum r, g, b, ray segments}
+  uint4 *it;           // {slice << 28 | pixel, next sample, slice end, -}
+  uint32_t *cand_cnt;  // filter survivors per ray (> kCandPlanes = overflow)
+  uint32_t *cand_idx;  // [kCandPlanes][n_slots] sphere indices, ascending
+};
+
+struct WaveRunInfo {
+  uint32_t launches, waves, n_slots;
+  int rays_per_lane, filter_grid, shade_grid;
+  bool rows_in_constant_bank, scene_in_smem;
+};
+
+size_t wave_pool_bytes(uint32_t n_slots);
+uint32_t wave_default_slots(int sm_count);
+void wave_carve(WaveParams &p, void *pool, uint32_t n_slots);
+// Runs one frame's slices: init, then shade/filter waves until no ray is left.  Synchronises
+// the stream (it polls the live-ray counter through host_live, pinned host memory).
+cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_count,
+                          size_t smem_optin_max, cudaStream_t st, unsigned int *host_live,
+                          WaveRunInfo *info);
+
+// Fused persistent form: one launch per frame; carves n_slots = grid * block * R out of the pool.
+cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
+                      int sm_count, size_t smem_optin_max, cudaStream_t st, WaveRunInfo *info);
+
 // rays_per_lane: 1, 2 or 4 (0 = default).  Launches the persistent path kernel.
 // host_rows: host copy of scene.fast (n_pad + 4 rows) or nullptr.
 cudaError_t launch_path(const PathParams &p, const float4 *host_rows, int rays_per_lane,

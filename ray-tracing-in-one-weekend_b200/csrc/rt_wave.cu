@@ -1,0 +1,595 @@
+// csrc/rt_wave.cu — wavefront form of the path-tracing hot path (sm_100a).
+//
+// The same arithmetic as the megakernel in rt_path.cu, cut into two kernels that alternate
+// over a pool of path slots resident in HBM/L2:
+//
+//   shade_kernel   one lane = one slot.  Finishes the ray segment traced in the previous wave:
+//                  f64 resolution of the filter's candidates (sphere::hit, src/cpu/sphere.h:24-51),
+//                  sky or material scatter (main.cc:12-30, material.h), then, if the path ended,
+//                  path regeneration: next sample of the slot's (pixel, slice) item or the next
+//                  item of the frame's work queue, camera::get_ray (camera.h:28-35).
+//   filter_kernel  one lane = R slots.  Conservative f32 line-sphere test of R rays against ALL
+//                  spheres in reference order (hittable_list::hit visits every object,
+//                  hittable_list.h:28-43): packed FFMA2, sphere rows through the constant bank
+//                  into uniform registers.  Survivors are appended to the slot's candidate
+//                  planes in ascending sphere order.  The lane carries no path state, only rays.
+//
+// The filter kernel is >85 % of the frame and nothing but the loop; the divergent, latency-bound
+// code (RNG, materials, f64) runs one slot per lane at full occupancy in the shade kernel.
+#include "rt_device.cuh"
+#include "rt_kernels.h"
+
+#include <cstdlib>
+#include <cstring>
+
+namespace rtb {
+
+#ifndef RTW_BLOCK
+#define RTW_BLOCK 256
+#endif
+#ifndef RTW_MINB
+#define RTW_MINB 3
+#endif
+constexpr int kWBlock = RTW_BLOCK;
+
+__device__ __forceinline__ float2 wffma2(float2 a, float2 b, float2 c) {
+  unsigned long long ra = *reinterpret_cast<unsigned long long *>(&a),
+                     rb = *reinterpret_cast<unsigned long long *>(&b),
+                     rc = *reinterpret_cast<unsigned long long *>(&c), rd;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+  return *reinterpret_cast<float2 *>(&rd);
+}
+__device__ __forceinline__ float2 wbc(float v) { return make_float2(v, v); }
+#define WPK(arr, r) (((r)&1) ? (arr)[(r) >> 1].y : (arr)[(r) >> 1].x)
+
+// ================================================================ filter
+// R rays per lane (even), G sphere rows per decision group.
+template <int R, int G, bool CROWS>
+__device__ __forceinline__ void filter_rays(const WaveParams &P, const ConstRows &CR, const uint32_t base,
+                                            const uint32_t stride) {
+  static_assert(R % 2 == 0, "rays are packed in pairs");
+  constexpr int NP = R / 2;
+  const uint32_t npad = P.scene.n_pad;
+  const float INF = __int_as_float(0x7f800000);
+  {
+    float2 DX[NP], DY[NP], DZ[NP], OX2[NP], OY2[NP], OZ2[NP], NOD[NP], OOT[NP];
+    uint32_t cnt[R], off[R];  // survivors so far / element offset of the next candidate plane
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      off[r] = base + r * stride;
+      const float4 o = P.ray_o[base + r * stride];  // {ox, oy, oz, |d| or < 0 = no ray}
+      const float4 d = P.ray_d[base + r * stride];  // unit direction
+      WPK(DX, r) = d.x; WPK(DY, r) = d.y; WPK(DZ, r) = d.z;
+      WPK(OX2, r) = 2.0f * o.x; WPK(OY2, r) = 2.0f * o.y; WPK(OZ2, r) = 2.0f * o.z;
+      WPK(NOD, r) = -(o.x * d.x + o.y * d.y + o.z * d.z);
+      // idle slots never pass the filter
+      WPK(OOT, r) = o.w > 0.0f ? (o.x * o.x + o.y * o.y + o.z * o.z) * (1.0f - RTB_FILTER_SLACK) : INF;
+      cnt[r] = 0;
+    }
+
+    // e = (c.d - o.d)^2 + (2 c.o + w) for one group of G rows; every FFMA2 multiplies by exactly
+    // one sphere scalar (a uniform register when CROWS)
+    auto group = [&](const float4 (&S)[G], float2 (&e)[G][NP]) {
+#pragma unroll
+      for (int k = 0; k < G; ++k)
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+          float2 b = wffma2(wbc(S[k].x), DX[p], wffma2(wbc(S[k].y), DY[p], wffma2(wbc(S[k].z), DZ[p], NOD[p])));
+          float2 e1 = wffma2(b, b, wbc(S[k].w));
+          e[k][p] = wffma2(wbc(S[k].x), OX2[p], wffma2(wbc(S[k].y), OY2[p], wffma2(wbc(S[k].z), OZ2[p], e1)));
+        }
+    };
+    // decision for one group: max over rows, one compare per ray, one vote, one branch
+    uint32_t *const cand = P.cand_idx;
+    const uint32_t nslots = P.n_slots;
+    auto decide = [&](const float2 (&e)[G][NP], uint32_t s0) {
+      bool any = false;
+#pragma unroll
+      for (int p = 0; p < NP; ++p) {
+        float mx = e[0][p].x, my = e[0][p].y;
+#pragma unroll
+        for (int k = 1; k < G; ++k) { mx = fmaxf(mx, e[k][p].x); my = fmaxf(my, e[k][p].y); }
+        any = any || mx >= OOT[p].x || my >= OOT[p].y;
+      }
+      if (__any_sync(0xffffffffu, any)) {
+#pragma unroll
+        for (int k = 0; k < G; ++k)
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+            if (WPK(e[k], r) >= WPK(OOT, r)) {
+              if (cnt[r] < kCandPlanes) cand[off[r]] = s0 + k;
+              off[r] += nslots;
+              cnt[r] += 1;
+            }
+      }
+    };
+
+    const float4 *frow = P.scene.fast;
+    float4 S[G];
+    float2 ea[G][NP], eb[G][NP];
+#pragma unroll
+    for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[k] : __ldg(frow + k);
+    group(S, ea);
+#pragma unroll
+    for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[G + k] : __ldg(frow + G + k);
+    uint32_t npad_r = npad;
+    asm volatile("" : "+r"(npad_r));
+    // software pipeline: the FFMA2s of group g+1 are issued before the decision on group g, so
+    // the max/compare/vote/branch chain never sits at the end of a dependency tail.  Two groups
+    // per trip (ea/eb ping-pong).  The row array carries 2G padding rows (w = -inf).
+    for (uint32_t s0 = 0; s0 < npad_r; s0 += 2 * G) {
+      group(S, eb);
+#pragma unroll
+      for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[s0 + 2 * G + k] : __ldg(frow + s0 + 2 * G + k);
+      decide(ea, s0);
+      group(S, ea);
+#pragma unroll
+      for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[s0 + 3 * G + k] : __ldg(frow + s0 + 3 * G + k);
+      decide(eb, s0 + G);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) P.cand_cnt[base + r * stride] = cnt[r];
+  }
+}
+
+template <int R, int G, bool CROWS>
+__global__ void __launch_bounds__(kWBlock, RTW_MINB)
+filter_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
+  const uint32_t stride = P.n_slots / R;  // slot of ray r = base + r * stride
+  // warp-uniform trip count (stride is a multiple of the block size): the sphere loop must stay
+  // convergent so that its rows can live in uniform registers
+  for (uint32_t blk = blockIdx.x; blk < stride / kWBlock; blk += gridDim.x)
+    filter_rays<R, G, CROWS>(P, CR, blk * kWBlock + threadIdx.x, stride);
+}
+
+// ================================================================ shade
+__device__ __forceinline__ double wave_dsqrt(double x) {  // see rt_path.cu fast_dsqrt
+  float xf = fmaxf((float)x, 1e-30f);
+  double y = (double)rsqrtf(xf);
+  double h = 0.5 * y;
+  double s = x * y;
+  s = fma(fma(-s, s, x), h, s);
+  s = fma(fma(-s, s, x), h, s);
+  return s;
+}
+
+struct WRay {
+  double ox, oy, oz, dx, dy, dz, a, tminA;
+};
+
+// sphere::hit on numerators (root = N / a, a common to the ray): src/cpu/sphere.h:24-51 with the
+// inclusive upper bound of hittable_list.h:34-39 (a later sphere with an equal root wins).
+__device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, double &bestN) {
+  double ocx = r.ox - S.x, ocy = r.oy - S.y, ocz = r.oz - S.z;
+  double half_b = ocx * r.dx + ocy * r.dy + ocz * r.dz;
+  double c = ocx * ocx + ocy * ocy + ocz * ocz - S.w * S.w;
+  double disc = half_b * half_b - r.a * c;
+  if (disc < 0.0) return false;
+  double sq = wave_dsqrt(disc);
+  double N = -half_b - sq;
+  if (N < r.tminA || bestN < N) {
+    N = -half_b + sq;
+    if (N < r.tminA || bestN < N) return false;
+  }
+  bestN = N;
+  return true;
+}
+
+// One slot, one wave: finish the traced ray segment (resolve + sky/scatter), regenerate the path
+// if it ended.  Returns 1 when the slot holds a ray for the next filter pass.
+__device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32_t i,
+                                               const double4 *exact, const float4 *mat,
+                                               const float2 *aux, const uint32_t npix,
+                                               const uint64_t total_items) {
+  float4 T = P.thr[i];  // {tr, tg, tb, depth}
+  int depth = __float_as_int(T.w);
+  if (depth < 0) return 0u;  // slot retired: the frame's work queue is empty
+  uint4 st = P.it[i];   // {item = slice << 28 | pixel (0xffffffff = none), samp, samp_end, -}
+  float4 A = P.acc[i];  // {sum r, sum g, sum b, ray segments} of the slot's item
+  float4 RO, RD;
+
+  if (depth > 0) {
+    // ---------------------------------------------------------- resolve + shade
+    RO = P.ray_o[i];
+    RD = P.ray_d[i];
+    A.w += 1.0f;  // one ray_color invocation (src/cpu/main.cc:12)
+    const float dx = RD.x, dy = RD.y, dz = RD.z;
+    WRay ray;
+    ray.ox = RO.x; ray.oy = RO.y; ray.oz = RO.z; ray.dx = dx; ray.dy = dy; ray.dz = dz;
+    ray.a = ray.dx * ray.dx + ray.dy * ray.dy + ray.dz * ray.dz;
+    ray.tminA = 0.001 * (double)RO.w * ray.a;  // main.cc:19 t_min in unit-direction units, times a
+    double bestN = __longlong_as_double(0x7ff0000000000000ll);
+    int id = -1;
+    const uint32_t cnt = P.cand_cnt[i];
+    if (cnt <= kCandPlanes) {
+      for (uint32_t k = 0; k < cnt; ++k) {
+        const uint32_t s = P.cand_idx[(size_t)k * P.n_slots + i];
+        if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+      }
+    } else {  // candidate planes overflowed: exact test of every sphere (rare)
+      for (uint32_t s = 0; s < P.scene.n; ++s)
+        if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+    }
+    if (id < 0) {
+      // sky, src/cpu/main.cc:27-29 (direction already unit length)
+      float t = 0.5f * (dy + 1.0f);
+      float w = 1.0f - t;
+      A.x += T.x * (w + t * 0.5f);
+      A.y += T.y * (w + t * 0.7f);
+      A.z += T.z * (w + t * 1.0f);
+      depth = 0;
+    } else {
+      // hit record, src/cpu/sphere.h:43-48 + hittable.h:16-19: point in f64, then narrowed
+      const double4 S = exact[id];
+      const double t = bestN * (2.0 - ray.a);  // 1/a = 2 - a to within eps^2 (a = 1 + eps)
+      const double px = ray.ox + t * ray.dx, py = ray.oy + t * ray.dy, pz = ray.oz + t * ray.dz;
+      const float2 ax = aux[id];  // {1/r (signed), kind}
+      float onx = (float)(px - S.x) * ax.x, ony = (float)(py - S.y) * ax.x,
+            onz = (float)(pz - S.z) * ax.x;
+      const bool front = (dx * onx + dy * ony + dz * onz) < 0.0f;
+      const float nx = front ? onx : -onx, ny = front ? ony : -ony, nz = front ? onz : -onz;
+      RO.x = (float)px; RO.y = (float)py; RO.z = (float)pz;
+
+      const uint32_t slot = P.max_depth - (uint32_t)depth + 1u;  // k-th hit of this path
+      const float4 xi = philox_uniforms(st.x & 0x0fffffffu, P.sample_offset + st.y - 1u, slot, P.seed);
+      const float4 M = mat[id];
+      const uint32_t kind = (uint32_t)__float_as_int(ax.y);
+      float sx, sy, sz;  // scattered direction (un-normalised, as in the reference)
+      bool alive = true;
+      if (kind == 0u) {
+        // lambertian::scatter, src/cpu/material.h:19-32
+        float ux, uy, uz;
+        unit_vector_from(xi.x, xi.y, ux, uy, uz);
+        sx = nx + ux; sy = ny + uy; sz = nz + uz;
+        if (fabsf(sx) < 1e-8f && fabsf(sy) < 1e-8f && fabsf(sz) < 1e-8f) { sx = nx; sy = ny; sz = nz; }
+        T.x *= M.x; T.y *= M.y; T.z *= M.z;
+      } else if (kind == 1u) {
+        // metal::scatter, src/cpu/material.h:40-46 (fuzz point drawn INSIDE the unit ball)
+        float dn = dx * nx + dy * ny + dz * nz;
+        sx = dx - 2.0f * dn * nx; sy = dy - 2.0f * dn * ny; sz = dz - 2.0f * dn * nz;
+        if (M.w > 0.0f) {
+          float ux, uy, uz;
+          unit_vector_from(xi.x, xi.y, ux, uy, uz);
+          float k = M.w * cbrtf(xi.z);
+          sx += k * ux; sy += k * uy; sz += k * uz;
+        }
+        alive = (sx * nx + sy * ny + sz * nz) > 0.0f;
+        T.x *= M.x; T.y *= M.y; T.z *= M.z;
+      } else {
+        // dielectric::scatter + reflectance + refract, src/cpu/material.h:57-87, vec3.h:126-131
+        float ratio = front ? (1.0f / M.w) : M.w;
+        float dn = dx * nx + dy * ny + dz * nz;
+        float cos_t = fminf(-dn, 1.0f);
+        float sin_t = sqrtf(fmaxf(0.0f, 1.0f - cos_t * cos_t));
+        bool reflect_it = ratio * sin_t > 1.0f;
+        if (!reflect_it) {
+          float r0 = (1.0f - ratio) / (1.0f + ratio);
+          r0 *= r0;
+          float x = 1.0f - cos_t, x2 = x * x;
+          reflect_it = (r0 + (1.0f - r0) * (x2 * x2 * x)) > xi.x;
+        }
+        if (reflect_it) {
+          sx = dx - 2.0f * dn * nx; sy = dy - 2.0f * dn * ny; sz = dz - 2.0f * dn * nz;
+        } else {
+          float ex = ratio * (dx + cos_t * nx), ey = ratio * (dy + cos_t * ny),
+                ez = ratio * (dz + cos_t * nz);
+          float k = -sqrtf(fabsf(1.0f - (ex * ex + ey * ey + ez * ez)));
+          sx = ex + k * nx; sy = ey + k * ny; sz = ez + k * nz;
+        }
+      }
+      depth -= 1;
+      if (!alive) depth = 0;  // absorbed (material.h:45); depth 0 = bounce limit (main.cc:16)
+      if (depth > 0) {
+        float len = sqrtf(sx * sx + sy * sy + sz * sz), inv = 1.0f / len;
+        RD.x = sx * inv; RD.y = sy * inv; RD.z = sz * inv;
+        RO.w = len;
+      }
+    }
+  }
+
+  if (depth == 0) {
+    // ------------------------------------------------------------ regenerate the path
+    while (st.y == st.z) {  // item exhausted: flush it and fetch the next
+      if (st.x != 0xffffffffu) {
+        P.accum[(size_t)(st.x >> 28) * npix + (st.x & 0x0fffffffu)] = A;
+        st.x = 0xffffffffu;
+      }
+      unsigned long long itq = atomicAdd(P.counter, 1ull);
+      if (itq >= total_items) { depth = -1; break; }
+      uint32_t sl = (uint32_t)(itq / npix);
+      uint32_t px = (uint32_t)(itq - (uint64_t)sl * npix);
+      sl += P.slice_begin;
+      st.x = sl << 28 | px;
+      // canonical slice k covers samples [floor(k*spp/8), floor((k+1)*spp/8))
+      st.y = (uint32_t)(((uint64_t)sl * P.spp) / RT_SLICES_DEV);
+      st.z = (uint32_t)(((uint64_t)(sl + 1) * P.spp) / RT_SLICES_DEV);
+      A = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (depth == 0) {
+      // camera::get_ray (src/cpu/camera.h:28-35) with pixel jitter (main.cc:116-117)
+      const uint32_t px = st.x & 0x0fffffffu;
+      const uint32_t row = px / P.width, ii = px - row * P.width;
+      const uint32_t j = P.height - 1 - row;
+      const float4 xi = philox_uniforms(px, P.sample_offset + st.y, 0u, P.seed);
+      st.y += 1;
+      float u = ((float)ii + xi.x) * P.cam.inv_wm1;
+      float v = ((float)j + xi.y) * P.cam.inv_hm1;
+      float rad = P.cam.lens_radius * sqrtf(xi.z), sn, cs;
+      sincospif(2.0f * xi.w, &sn, &cs);
+      float rdx = rad * cs, rdy = rad * sn;
+      float offx = P.cam.u[0] * rdx + P.cam.v[0] * rdy;
+      float offy = P.cam.u[1] * rdx + P.cam.v[1] * rdy;
+      float offz = P.cam.u[2] * rdx + P.cam.v[2] * rdy;
+      RO.x = P.cam.origin[0] + offx;
+      RO.y = P.cam.origin[1] + offy;
+      RO.z = P.cam.origin[2] + offz;
+      float ddx = P.cam.llc_minus_origin[0] + u * P.cam.horizontal[0] + v * P.cam.vertical[0] - offx;
+      float ddy = P.cam.llc_minus_origin[1] + u * P.cam.horizontal[1] + v * P.cam.vertical[1] - offy;
+      float ddz = P.cam.llc_minus_origin[2] + u * P.cam.horizontal[2] + v * P.cam.vertical[2] - offz;
+      float len = sqrtf(ddx * ddx + ddy * ddy + ddz * ddz), inv = 1.0f / len;
+      RD.x = ddx * inv; RD.y = ddy * inv; RD.z = ddz * inv; RD.w = 0.f;
+      RO.w = len;
+      T.x = T.y = T.z = 1.0f;
+      depth = (int)P.max_depth;
+    }
+  }
+
+  if (depth > 0) {
+    P.ray_o[i] = RO;
+    P.ray_d[i] = RD;
+  } else {
+    P.ray_o[i] = make_float4(0.f, 0.f, 0.f, -1.0f);  // no ray: the filter skips the slot
+  }
+  T.w = __int_as_float(depth);
+  P.thr[i] = T;
+  P.acc[i] = A;
+  P.it[i] = st;
+  return depth > 0 ? 1u : 0u;
+}
+
+// per-hit scene rows -> shared memory: 1-D bulk (TMA) copies completing on an mbarrier
+__device__ __forceinline__ void stage_hit_rows(const WaveParams &P, unsigned char *smem_raw,
+                                               uint64_t *bar, const double4 *&exact,
+                                               const float4 *&mat, const float2 *&aux) {
+  const uint32_t npad = P.scene.n_pad;
+  double4 *s_exact = reinterpret_cast<double4 *>(smem_raw);
+  float4 *s_mat = reinterpret_cast<float4 *>(smem_raw + (size_t)npad * 32);
+  float2 *s_aux = reinterpret_cast<float2 *>(smem_raw + (size_t)npad * 48);
+  if (threadIdx.x == 0) mbar_init(bar, 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(bar, npad * 56u);
+    const uint32_t kChunk = 32768u;
+    const unsigned char *src[3] = {reinterpret_cast<const unsigned char *>(P.scene.exact),
+                                   reinterpret_cast<const unsigned char *>(P.scene.mat),
+                                   reinterpret_cast<const unsigned char *>(P.scene.aux)};
+    unsigned char *dst[3] = {reinterpret_cast<unsigned char *>(s_exact),
+                             reinterpret_cast<unsigned char *>(s_mat),
+                             reinterpret_cast<unsigned char *>(s_aux)};
+    const uint32_t len[3] = {npad * 32u, npad * 16u, npad * 8u};
+    for (int a = 0; a < 3; ++a)
+      for (uint32_t off = 0; off < len[a]; off += kChunk)
+        bulk_g2s(dst[a] + off, src[a] + off, min(kChunk, len[a] - off), bar);
+  }
+  mbar_wait(bar, 0);
+  exact = s_exact; mat = s_mat; aux = s_aux;
+}
+
+template <bool SMEM>
+__global__ void __launch_bounds__(256, 4)
+shade_kernel(const __grid_constant__ WaveParams P) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t s_bar;
+  const double4 *exact = P.scene.exact;
+  const float4 *mat = P.scene.mat;
+  const float2 *aux = P.scene.aux;
+  if (SMEM) stage_hit_rows(P, smem_raw, &s_bar, exact, mat, aux);
+  const uint32_t npix = P.width * P.height;
+  const uint64_t total_items = (uint64_t)npix * (P.slice_end - P.slice_begin);
+  uint32_t live_lanes = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_slots; i += gridDim.x * blockDim.x)
+    live_lanes += shade_slot(P, i, exact, mat, aux, npix, total_items);
+  // live rays of the next wave (the host stops the frame when this stays 0)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) live_lanes += __shfl_xor_sync(0xffffffffu, live_lanes, o);
+  if ((threadIdx.x & 31) == 0 && live_lanes) atomicAdd(P.live, live_lanes);
+}
+
+// ================================================================ fused persistent form
+// Every lane owns R slots for the whole frame and alternates shade (one slot at a time, rolled
+// loop, state in the pool) and filter (R rays at once, registers hold nothing but rays).  No
+// kernel boundary, no inter-lane dependency; warps of an SM drift apart, so the latency-bound
+// shade phases of some warps overlap the FMA-pipe-bound filter phases of the others.
+template <int R, int G, bool CROWS, bool SMEM>
+__global__ void __launch_bounds__(kWBlock, RTW_MINB)
+fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t s_bar;
+  const double4 *exact = P.scene.exact;
+  const float4 *mat = P.scene.mat;
+  const float2 *aux = P.scene.aux;
+  if (SMEM) stage_hit_rows(P, smem_raw, &s_bar, exact, mat, aux);
+  const uint32_t npix = P.width * P.height;
+  const uint64_t total_items = (uint64_t)npix * (P.slice_end - P.slice_begin);
+  const uint32_t stride = P.n_slots / R;
+  const uint32_t base = blockIdx.x * kWBlock + threadIdx.x;  // grid * block == stride
+#pragma unroll 1
+  for (int r = 0; r < R; ++r) {
+    const uint32_t i = base + r * stride;
+    P.thr[i] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));  // depth 0: needs a path
+    P.acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    P.it[i] = make_uint4(0xffffffffu, 0u, 0u, 0u);
+  }
+  for (;;) {
+    uint32_t live = 0;
+#pragma unroll 1
+    for (int r = 0; r < R; ++r) live += shade_slot(P, base + r * stride, exact, mat, aux, npix, total_items);
+    if (__all_sync(0xffffffffu, live == 0u)) break;  // warp-uniform exit keeps the loop convergent
+    filter_rays<R, G, CROWS>(P, CR, base, stride);
+  }
+}
+
+__global__ void __launch_bounds__(256) wave_init_kernel(const __grid_constant__ WaveParams P) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_slots; i += gridDim.x * blockDim.x) {
+    P.thr[i] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));  // depth 0: needs a path
+    P.acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    P.it[i] = make_uint4(0xffffffffu, 0u, 0u, 0u);
+    P.ray_o[i] = make_float4(0.f, 0.f, 0.f, -1.0f);
+    P.ray_d[i] = make_float4(0.f, 1.f, 0.f, 0.f);
+    P.cand_cnt[i] = 0;
+  }
+}
+
+// ================================================================ host side
+size_t wave_pool_bytes(uint32_t n_slots) {
+  // ray_o, ray_d, thr, acc (float4) + it (uint4) + cand_cnt + cand_idx planes
+  return (size_t)n_slots * (5 * 16 + 4 + 4 * (size_t)kCandPlanes);
+}
+
+uint32_t wave_default_slots(int sm_count) {
+  // a whole number of filter-kernel rounds: SMs x resident lanes x rays per lane x rounds
+  // (also the capacity the fused kernel needs at R = 4)
+  return (uint32_t)sm_count * RTW_MINB * kWBlock * 2u * 2u;
+}
+
+void wave_carve(WaveParams &p, void *pool, uint32_t n_slots) {
+  unsigned char *b = static_cast<unsigned char *>(pool);
+  size_t n = n_slots;
+  p.n_slots = n_slots;
+  p.ray_o = reinterpret_cast<float4 *>(b); b += n * 16;
+  p.ray_d = reinterpret_cast<float4 *>(b); b += n * 16;
+  p.thr = reinterpret_cast<float4 *>(b); b += n * 16;
+  p.acc = reinterpret_cast<float4 *>(b); b += n * 16;
+  p.it = reinterpret_cast<uint4 *>(b); b += n * 16;
+  p.cand_cnt = reinterpret_cast<uint32_t *>(b); b += n * 4;
+  p.cand_idx = reinterpret_cast<uint32_t *>(b);
+}
+
+template <int R, int G>
+static cudaError_t launch_filter_t(const WaveParams &p, const ConstRows &cr, bool crows, int grid,
+                                   cudaStream_t st) {
+  if (crows)
+    filter_kernel<R, G, true><<<grid, kWBlock, 0, st>>>(p, cr);
+  else
+    filter_kernel<R, G, false><<<grid, kWBlock, 0, st>>>(p, cr);
+  return cudaGetLastError();
+}
+
+cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_count,
+                          size_t smem_optin_max, cudaStream_t st, unsigned int *host_live,
+                          WaveRunInfo *info) {
+  static ConstRows cr;
+  const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
+                     !getenv("RT_B200_NO_CONST_ROWS");
+  if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
+  int rpl = 2;
+  if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
+  if (rpl != 2 && rpl != 4) return cudaErrorInvalidValue;
+  if (p.n_slots % (kWBlock * 4u)) return cudaErrorInvalidValue;
+
+  // shade kernel: per-hit rows in shared memory when they fit
+  const size_t scene_smem = (size_t)p.scene.n_pad * 56;
+  const bool in_smem = scene_smem + 1024 <= smem_optin_max / 4;
+  cudaError_t e;
+  if (in_smem) {
+    e = cudaFuncSetAttribute(shade_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scene_smem);
+    if (e != cudaSuccess) return e;
+  }
+  int shade_per_sm = 0;
+  e = in_smem ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&shade_per_sm, shade_kernel<true>, 256, scene_smem)
+              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&shade_per_sm, shade_kernel<false>, 256, 0);
+  if (e != cudaSuccess) return e;
+  if (shade_per_sm < 1) return cudaErrorLaunchOutOfResources;
+  const int shade_grid = sm_count * shade_per_sm;
+  const int filter_grid = sm_count * RTW_MINB;
+
+  auto shade = [&]() -> cudaError_t {
+    if (in_smem) shade_kernel<true><<<shade_grid, 256, scene_smem, st>>>(p);
+    else shade_kernel<false><<<shade_grid, 256, 0, st>>>(p);
+    return cudaGetLastError();
+  };
+  auto filter = [&]() -> cudaError_t {
+    return rpl == 4 ? launch_filter_t<4, 4>(p, cr, crows, filter_grid, st)
+                    : launch_filter_t<2, 4>(p, cr, crows, filter_grid, st);
+  };
+
+  uint32_t launches = 0, waves = 0;
+  wave_init_kernel<<<sm_count * 4, 256, 0, st>>>(p);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  ++launches;
+
+  // every sample needs at least one wave of its slot: no need to poll before that many waves
+  uint64_t total_samples = 0;
+  for (uint32_t k = p.slice_begin; k < p.slice_end; ++k)
+    total_samples += ((uint64_t)(k + 1) * p.spp) / RT_SLICES_DEV - ((uint64_t)k * p.spp) / RT_SLICES_DEV;
+  total_samples *= (uint64_t)p.width * p.height;
+  const uint64_t min_waves = total_samples / p.n_slots;
+  const uint32_t poll_every = 4;
+
+  for (;;) {
+    const bool poll = waves >= min_waves && (waves - min_waves) % poll_every == 0;
+    if (poll && (e = cudaMemsetAsync(p.live, 0, sizeof(unsigned int), st)) != cudaSuccess) return e;
+    if ((e = shade()) != cudaSuccess) return e;
+    ++launches;
+    if (poll) {
+      if ((e = cudaMemcpyAsync(host_live, p.live, sizeof(unsigned int), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+      if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+      if (*host_live == 0) break;
+    }
+    if ((e = filter()) != cudaSuccess) return e;
+    ++launches;
+    ++waves;
+  }
+  if (info) {
+    info->launches = launches; info->waves = waves; info->n_slots = p.n_slots;
+    info->rays_per_lane = rpl; info->filter_grid = filter_grid; info->shade_grid = shade_grid;
+    info->rows_in_constant_bank = crows; info->scene_in_smem = in_smem;
+  }
+  return cudaSuccess;
+}
+
+template <int R, int G>
+static cudaError_t launch_fused_t(const WaveParams &p, const ConstRows &cr, bool crows, bool in_smem,
+                                  size_t smem, int grid, cudaStream_t st) {
+#define RTW_FUSED(CR_, SM_)                                                                        \
+  do {                                                                                             \
+    auto k = fused_kernel<R, G, CR_, SM_>;                                                         \
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    if (e != cudaSuccess) return e;                                                                \
+    k<<<grid, kWBlock, smem, st>>>(p, cr);                                                         \
+  } while (0)
+  if (crows && in_smem) RTW_FUSED(true, true);
+  else if (crows) RTW_FUSED(true, false);
+  else if (in_smem) RTW_FUSED(false, true);
+  else RTW_FUSED(false, false);
+#undef RTW_FUSED
+  return cudaGetLastError();
+}
+
+cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
+                      int sm_count, size_t smem_optin_max, cudaStream_t st, WaveRunInfo *info) {
+  static ConstRows cr;
+  const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
+                     !getenv("RT_B200_NO_CONST_ROWS");
+  if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
+  int rpl = 2;
+  if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
+  if (rpl != 2 && rpl != 4) return cudaErrorInvalidValue;
+  const int grid = sm_count * RTW_MINB;
+  const uint32_t n_slots = (uint32_t)grid * kWBlock * (uint32_t)rpl;
+  if (n_slots > pool_slots) return cudaErrorInvalidValue;
+  wave_carve(p, pool, n_slots);
+  const size_t scene_smem = (size_t)p.scene.n_pad * 56;
+  const bool in_smem = (scene_smem + 1024) * RTW_MINB <= smem_optin_max;
+  const size_t smem = in_smem ? scene_smem : 0;
+  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, cr, crows, in_smem, smem, grid, st)
+                           : launch_fused_t<2, 4>(p, cr, crows, in_smem, smem, grid, st);
+  if (info) {
+    info->launches = 1; info->waves = 0; info->n_slots = n_slots; info->rays_per_lane = rpl;
+    info->filter_grid = grid; info->shade_grid = 0; info->rows_in_constant_bank = crows;
+    info->scene_in_smem = in_smem;
+  }
+  return e;
+}
+
+}  // namespace rtb
