@@ -31,7 +31,7 @@ extern "C" {
 #define RT_METAL 1u      /* src/cpu/material.h:36-51 */
 #define RT_DIELECTRIC 2u /* src/cpu/material.h:53-87 */
 
-#define RT_SLICES 8u /* canonical sample slices per pixel (multi-GPU split) */
+#define RT_SLICES 64u /* canonical sample slices per pixel (multi-GPU split) */
 
 /* One sphere with its material, in the reference's insertion order
  * (hittable_list::add(make_shared<sphere>(center, radius, material)),

@@ -18,7 +18,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
-SLICES = 8
+SLICES = 64
 FLAG_COUNT_RAYS = 1
 
 

@@ -212,7 +212,7 @@ static CameraF32 narrow_camera(const CamFrame &f, uint32_t W, uint32_t H) {
 extern "C" int rt_frame_create(uint32_t width, uint32_t height, int32_t device, rt_frame **out) {
   if (!out) return fail(RT_E_INVALID, "out is NULL");
   *out = nullptr;
-  if (width < 2 || height < 2 || (uint64_t)width * height >= (1ull << 28))
+  if (width < 2 || height < 2 || (uint64_t)width * height >= (1ull << kItemShift))
     return fail(RT_E_INVALID, "image size %ux%u out of range (min 2x2)", width, height);
   CU(cudaSetDevice(device));
   rt_frame *f = new (std::nothrow) rt_frame();

@@ -19,7 +19,7 @@
 namespace rtb {
 
 // ---------------------------------------------------------------- slice tree + finalise
-// Canonical pairwise tree over RT_SLICES = 8 slices: ((s0+s1)+(s2+s3))+((s4+s5)+(s6+s7)).
+// Canonical pairwise tree over the RT_SLICES = 64 slices: ((s0+s1)+(s2+s3))+((s4+s5)+(s6+s7)) ...
 // A GPU that rendered an aligned power-of-two block of slices sums exactly its sub-tree;
 // the finalise kernel adds the remaining upper levels over the per-GPU partials in rank
 // order.  Every fp32 addition is therefore the same, in the same order, for 1/2/4/8 GPUs.
@@ -40,13 +40,24 @@ struct PtrPack {
   const float4 *p[8];
 };
 
+// the same tree over N consecutive slice planes of one accumulation buffer
 template <int N>
-__global__ void __launch_bounds__(256) reduce_local_kernel(const __grid_constant__ PtrPack src,
+__device__ __forceinline__ float4 tree_sum_planes(const float4 *base, size_t plane, size_t i) {
+  if constexpr (N == 1) {
+    return __ldcs(base + i);
+  } else {
+    return add4(tree_sum_planes<N / 2>(base, plane, i),
+                tree_sum_planes<N / 2>(base + (N / 2) * plane, plane, i));
+  }
+}
+
+template <int N>
+__global__ void __launch_bounds__(256) reduce_local_kernel(const float4 *__restrict__ first_plane,
                                                            float4 *__restrict__ dst,
                                                            uint32_t npix) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < npix;
        i += (size_t)gridDim.x * blockDim.x)
-    dst[i] = tree_sum<N>(src.p, i);
+    dst[i] = tree_sum_planes<N>(first_plane, npix, i);
 }
 
 // write_color, src/cpu/color.h:8-23: x = sqrt(sum/spp); int(256 * clamp(x, 0, 0.999)).
@@ -189,14 +200,16 @@ static int grid_for(uint32_t work_items, int sm_count, int per_sm = 8) {
 cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t slice_begin,
                                 uint32_t slice_end, float4 *dst, int sm_count, cudaStream_t st) {
   uint32_t cnt = slice_end - slice_begin;
-  PtrPack pk{};
-  for (uint32_t k = 0; k < cnt && k < 8; ++k) pk.p[k] = accum + (size_t)(slice_begin + k) * npix;
+  const float4 *pk = accum + (size_t)slice_begin * npix;
   int grid = grid_for(npix, sm_count);
   switch (cnt) {
     case 1: reduce_local_kernel<1><<<grid, 256, 0, st>>>(pk, dst, npix); break;
     case 2: reduce_local_kernel<2><<<grid, 256, 0, st>>>(pk, dst, npix); break;
     case 4: reduce_local_kernel<4><<<grid, 256, 0, st>>>(pk, dst, npix); break;
     case 8: reduce_local_kernel<8><<<grid, 256, 0, st>>>(pk, dst, npix); break;
+    case 16: reduce_local_kernel<16><<<grid, 256, 0, st>>>(pk, dst, npix); break;
+    case 32: reduce_local_kernel<32><<<grid, 256, 0, st>>>(pk, dst, npix); break;
+    case 64: reduce_local_kernel<64><<<grid, 256, 0, st>>>(pk, dst, npix); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();

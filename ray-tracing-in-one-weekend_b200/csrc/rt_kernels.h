@@ -6,7 +6,10 @@
 
 #include "rt_device.cuh"
 
-#define RT_SLICES_DEV 8u
+#define RT_SLICES_DEV 64u  // == RT_SLICES (include/rt_b200.h)
+// work item = slice << kItemShift | pixel (0xffffffff = none)
+constexpr unsigned kItemShift = 26;
+constexpr unsigned kItemPixelMask = (1u << kItemShift) - 1u;
 
 // Scene rows are padded to a multiple of kRowPad (padding rows never pass the filter) and the
 // filter-row array carries kRowTail more padding rows for the loop's prefetch.
@@ -59,7 +62,7 @@ struct WaveParams {
   float4 *ray_d;       // {unit direction, -}
   float4 *thr;         // {throughput r, g, b, depth (int bits): >0 bounces left, 0 new path, -1 retired}
   float4 *acc;         // {item sum r, g, b, ray segments}
-  uint4 *it;           // {slice << 28 | pixel, next sample, slice end, -}
+  uint4 *it;           // {slice << kItemShift | pixel, next sample, slice end, -}
   uint32_t *cand_cnt;  // filter survivors per ray (> kCandPlanes = overflow)
   uint32_t *cand_idx;  // [kCandPlanes][n_slots] sphere indices, ascending
 };

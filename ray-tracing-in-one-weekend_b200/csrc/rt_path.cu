@@ -193,7 +193,7 @@ path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstR
   float tr[R], tg[R], tb[R];      // path throughput (product of attenuations)
   float ar[R], ag[R], ab[R];      // item accumulator (sum over the slice's samples)
   float nrays[R];                 // ray segments traced for this item
-  uint32_t item[R];               // slice << 28 | pixel; 0xffffffff = no item yet
+  uint32_t item[R];               // slice << kItemShift | pixel; 0xffffffff = no item yet
   uint32_t samp[R], samp_end[R];  // next sample / end of the slice (frame-relative)
   int depth[R];                   // > 0 bounces left (main.cc:16); 0 = needs a path; -1 = dead
 #pragma unroll
@@ -215,7 +215,7 @@ path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstR
       if (depth[r] == 0) {
         while (samp[r] == samp_end[r]) {  // item exhausted: flush it and fetch the next
           if (item[r] != 0xffffffffu) {
-            P.accum[(size_t)(item[r] >> 28) * npix + (item[r] & 0x0fffffffu)] =
+            P.accum[(size_t)(item[r] >> kItemShift) * npix + (item[r] & kItemPixelMask)] =
                 make_float4(ar[r], ag[r], ab[r], nrays[r]);
             item[r] = 0xffffffffu;
           }
@@ -224,15 +224,15 @@ path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstR
           uint32_t sl = (uint32_t)(it / npix);
           uint32_t px = (uint32_t)(it - (uint64_t)sl * npix);
           sl += P.slice_begin;
-          item[r] = sl << 28 | px;
-          // canonical slice k covers samples [floor(k*spp/8), floor((k+1)*spp/8))
+          item[r] = sl << kItemShift | px;
+          // canonical slice k covers samples [floor(k*spp/S), floor((k+1)*spp/S)), S = RT_SLICES
           samp[r] = (uint32_t)(((uint64_t)sl * P.spp) / RT_SLICES_DEV);
           samp_end[r] = (uint32_t)(((uint64_t)(sl + 1) * P.spp) / RT_SLICES_DEV);
           ar[r] = ag[r] = ab[r] = 0.f; nrays[r] = 0.f;
         }
         if (depth[r] == 0) {
           // camera::get_ray (src/cpu/camera.h:28-35) with pixel jitter (main.cc:116-117)
-          const uint32_t px = item[r] & 0x0fffffffu;
+          const uint32_t px = item[r] & kItemPixelMask;
           const uint32_t row = px / P.width, i = px - row * P.width;
           const uint32_t j = P.height - 1 - row;
           const float4 xi = philox_uniforms(px, P.sample_offset + samp[r], 0u, P.seed);
@@ -401,7 +401,7 @@ path_kernel(const __grid_constant__ PathParams P, const __grid_constant__ ConstR
 
       const uint32_t slot = P.max_depth - (uint32_t)depth[r] + 1u;  // k-th hit of this path
       const float4 xi =
-          philox_uniforms(item[r] & 0x0fffffffu, P.sample_offset + samp[r] - 1u, slot, P.seed);
+          philox_uniforms(item[r] & kItemPixelMask, P.sample_offset + samp[r] - 1u, slot, P.seed);
       const float4 M = mat[id];
       const uint32_t kind = (uint32_t)__float_as_int(ax.y);
       float sx, sy, sz;  // scattered direction (un-normalised, as in the reference)

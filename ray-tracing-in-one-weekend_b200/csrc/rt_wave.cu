@@ -89,7 +89,7 @@ __device__ __forceinline__ void filter_rays(const WaveParams &P, const ConstRows
         float mx = e[0][p].x, my = e[0][p].y;
 #pragma unroll
         for (int k = 1; k < G; ++k) { mx = fmaxf(mx, e[k][p].x); my = fmaxf(my, e[k][p].y); }
-        any = any || mx >= OOT[p].x || my >= OOT[p].y;
+        any = any | (mx >= OOT[p].x) | (my >= OOT[p].y);  // no short-circuit: independent compares
       }
       if (__any_sync(0xffffffffu, any)) {
 #pragma unroll
@@ -184,7 +184,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
   float4 T = P.thr[i];  // {tr, tg, tb, depth}
   int depth = __float_as_int(T.w);
   if (depth < 0) return 0u;  // slot retired: the frame's work queue is empty
-  uint4 st = P.it[i];   // {item = slice << 28 | pixel (0xffffffff = none), samp, samp_end, -}
+  uint4 st = P.it[i];   // {item = slice << kItemShift | pixel (0xffffffff = none), samp, samp_end, -}
   float4 A = P.acc[i];  // {sum r, sum g, sum b, ray segments} of the slot's item
   float4 RO, RD;
 
@@ -231,7 +231,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       RO.x = (float)px; RO.y = (float)py; RO.z = (float)pz;
 
       const uint32_t slot = P.max_depth - (uint32_t)depth + 1u;  // k-th hit of this path
-      const float4 xi = philox_uniforms(st.x & 0x0fffffffu, P.sample_offset + st.y - 1u, slot, P.seed);
+      const float4 xi = philox_uniforms(st.x & kItemPixelMask, P.sample_offset + st.y - 1u, slot, P.seed);
       const float4 M = mat[id];
       const uint32_t kind = (uint32_t)__float_as_int(ax.y);
       float sx, sy, sz;  // scattered direction (un-normalised, as in the reference)
@@ -291,7 +291,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
     // ------------------------------------------------------------ regenerate the path
     while (st.y == st.z) {  // item exhausted: flush it and fetch the next
       if (st.x != 0xffffffffu) {
-        P.accum[(size_t)(st.x >> 28) * npix + (st.x & 0x0fffffffu)] = A;
+        P.accum[(size_t)(st.x >> kItemShift) * npix + (st.x & kItemPixelMask)] = A;
         st.x = 0xffffffffu;
       }
       unsigned long long itq = atomicAdd(P.counter, 1ull);
@@ -299,15 +299,15 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       uint32_t sl = (uint32_t)(itq / npix);
       uint32_t px = (uint32_t)(itq - (uint64_t)sl * npix);
       sl += P.slice_begin;
-      st.x = sl << 28 | px;
-      // canonical slice k covers samples [floor(k*spp/8), floor((k+1)*spp/8))
+      st.x = sl << kItemShift | px;
+      // canonical slice k covers samples [floor(k*spp/S), floor((k+1)*spp/S)), S = RT_SLICES
       st.y = (uint32_t)(((uint64_t)sl * P.spp) / RT_SLICES_DEV);
       st.z = (uint32_t)(((uint64_t)(sl + 1) * P.spp) / RT_SLICES_DEV);
       A = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (depth == 0) {
       // camera::get_ray (src/cpu/camera.h:28-35) with pixel jitter (main.cc:116-117)
-      const uint32_t px = st.x & 0x0fffffffu;
+      const uint32_t px = st.x & kItemPixelMask;
       const uint32_t row = px / P.width, ii = px - row * P.width;
       const uint32_t j = P.height - 1 - row;
       const float4 xi = philox_uniforms(px, P.sample_offset + st.y, 0u, P.seed);

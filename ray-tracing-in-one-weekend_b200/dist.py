@@ -4,10 +4,10 @@ The reference has no multi-device path; the rule here is the no
 each GPU renders a slice of the samples of EVERY pixel, partial sums travel to rank 0, and the
 image must not depend on the GPU count.  That is achieved without arithmetic in flight:
 
-  * the samples of a pixel are cut into SLICES = 8 canonical slices
-    [floor(k*spp/8), floor((k+1)*spp/8)); the path kernel sums each slice sequentially,
-  * rank g of G (G in 1, 2, 4, 8) owns the aligned block of 8/G slices `slice_block(g, G)` and
-    pre-sums exactly that sub-tree of ((s0+s1)+(s2+s3))+((s4+s5)+(s6+s7)) on its own GPU,
+  * the samples of a pixel are cut into SLICES = 64 canonical slices
+    [floor(k*spp/64), floor((k+1)*spp/64)); the path kernel sums each slice sequentially,
+  * rank g of G (G in 1, 2, 4, 8) owns the aligned block of 64/G slices `slice_block(g, G)` and
+    pre-sums exactly that sub-tree of the pairwise tree ((s0+s1)+(s2+s3))+... on its own GPU,
   * the [H*W] float4 partials are GATHERED to rank 0 in rank order (NCCL send/recv over
     NVLink: bytes only), and rank 0's finalise kernel adds the remaining upper levels of the
     same tree, fused with write_color (src/cpu/color.h:8-23).
@@ -18,7 +18,7 @@ torch.distributed backend, which is how the world_size-2 `gloo` tests on CPU cov
 """
 from __future__ import annotations
 
-SLICES = 8
+SLICES = 64
 
 
 def slice_block(rank: int, world: int) -> tuple[int, int]:

@@ -17,14 +17,18 @@ def tree(parts):
     return parts[0]
 
 
+NSLICES = 64  # == rt_b200.dist.SLICES (asserted below)
+
+
 def synthetic_slices(npix, seed=5):
     rng = np.random.default_rng(seed)
     # magnitudes that make fp32 addition order matter
-    return (rng.random((8, npix, 4), dtype=np.float32) * np.float32(300.0)).astype(np.float32)
+    return (rng.random((NSLICES, npix, 4), dtype=np.float32) * np.float32(300.0)).astype(np.float32)
 
 
 def test_slice_blocks_partition_the_frame(rt):
     from rt_b200 import dist as rd
+    assert rd.SLICES == NSLICES == rt.SLICES
     for G in (1, 2, 4, 8):
         blocks = [rd.slice_block(r, G) for r in range(G)]
         assert blocks[0][0] == 0 and blocks[-1][1] == rd.SLICES
@@ -36,7 +40,7 @@ def test_slice_blocks_partition_the_frame(rt):
     with pytest.raises(ValueError):
         rd.slice_block(2, 2)
     # ragged spp: slices differ by at most one sample and tile [0, spp)
-    edges = [rd.slice_samples(k, 13) for k in range(8)]
+    edges = [rd.slice_samples(k, 13) for k in range(rd.SLICES)]
     assert edges[0][0] == 0 and edges[-1][1] == 13
     assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
 
@@ -45,12 +49,12 @@ def test_tree_is_rank_count_invariant():
     s = synthetic_slices(4096)
     full = tree(list(s))
     for G in (2, 4, 8):
-        per = 8 // G
+        per = NSLICES // G
         partials = [tree(list(s[g * per:(g + 1) * per])) for g in range(G)]
         assert np.array_equal(tree(partials), full)
     # a plain left-to-right sum is NOT what the tree computes (so the test can fail)
     seq = s[0].copy()
-    for k in range(1, 8):
+    for k in range(1, NSLICES):
         seq = seq + s[k]
     assert not np.array_equal(seq, full)
 
