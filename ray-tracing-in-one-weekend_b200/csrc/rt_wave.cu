@@ -175,8 +175,11 @@ __device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, d
   return true;
 }
 
-// One slot, one wave: finish the traced ray segment (resolve + sky/scatter), regenerate the path
-// if it ended.  Returns 1 when the slot holds a ray for the next filter pass.
+// One slot, one wave.  (1) Finish the ray segment traced by the last filter pass: f64 resolution
+// of its candidates, sky on a miss.  (2) ONE Philox block per slot and wave: the camera sample of
+// a new path (miss / empty slot) or the scatter sample of the hit.  (3) camera::get_ray or
+// material::scatter.  A path that ends at a hit (absorbed, bounce limit) leaves the slot without a
+// ray for one wave and regenerates in the next one.  Returns 0 once the slot is retired.
 __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32_t i,
                                                const double4 *exact, const float4 *mat,
                                                const float2 *aux, const uint32_t npix,
@@ -186,20 +189,20 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
   if (depth < 0) return 0u;  // slot retired: the frame's work queue is empty
   uint4 st = P.it[i];   // {item = slice << kItemShift | pixel (0xffffffff = none), samp, samp_end, -}
   float4 A = P.acc[i];  // {sum r, sum g, sum b, ray segments} of the slot's item
-  float4 RO, RD;
+  float4 RO = make_float4(0.f, 0.f, 0.f, -1.f), RD = make_float4(0.f, 1.f, 0.f, 0.f);
+  int id = -1;
+  double hpx = 0, hpy = 0, hpz = 0;  // hit point (f64)
 
   if (depth > 0) {
-    // ---------------------------------------------------------- resolve + shade
+    // ---------------------------------------------------------- resolve
     RO = P.ray_o[i];
     RD = P.ray_d[i];
     A.w += 1.0f;  // one ray_color invocation (src/cpu/main.cc:12)
-    const float dx = RD.x, dy = RD.y, dz = RD.z;
     WRay ray;
-    ray.ox = RO.x; ray.oy = RO.y; ray.oz = RO.z; ray.dx = dx; ray.dy = dy; ray.dz = dz;
+    ray.ox = RO.x; ray.oy = RO.y; ray.oz = RO.z; ray.dx = RD.x; ray.dy = RD.y; ray.dz = RD.z;
     ray.a = ray.dx * ray.dx + ray.dy * ray.dy + ray.dz * ray.dz;
     ray.tminA = 0.001 * (double)RO.w * ray.a;  // main.cc:19 t_min in unit-direction units, times a
     double bestN = __longlong_as_double(0x7ff0000000000000ll);
-    int id = -1;
     const uint32_t cnt = P.cand_cnt[i];
     if (cnt <= kCandPlanes) {
       for (uint32_t k = 0; k < cnt; ++k) {
@@ -212,53 +215,105 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
     }
     if (id < 0) {
       // sky, src/cpu/main.cc:27-29 (direction already unit length)
-      float t = 0.5f * (dy + 1.0f);
+      float t = 0.5f * (RD.y + 1.0f);
       float w = 1.0f - t;
       A.x += T.x * (w + t * 0.5f);
       A.y += T.y * (w + t * 0.7f);
       A.z += T.z * (w + t * 1.0f);
       depth = 0;
     } else {
-      // hit record, src/cpu/sphere.h:43-48 + hittable.h:16-19: point in f64, then narrowed
-      const double4 S = exact[id];
       const double t = bestN * (2.0 - ray.a);  // 1/a = 2 - a to within eps^2 (a = 1 + eps)
-      const double px = ray.ox + t * ray.dx, py = ray.oy + t * ray.dy, pz = ray.oz + t * ray.dz;
+      hpx = ray.ox + t * ray.dx; hpy = ray.oy + t * ray.dy; hpz = ray.oz + t * ray.dz;
+    }
+  }
+
+  const bool regen = depth == 0;
+  if (regen) {
+    // ------------------------------------------------------------ next sample / next item
+    while (st.y == st.z) {  // item exhausted: flush it and fetch the next
+      if (st.x != 0xffffffffu) {
+        P.accum[(size_t)(st.x >> kItemShift) * npix + (st.x & kItemPixelMask)] = A;
+        st.x = 0xffffffffu;
+      }
+      unsigned long long itq = atomicAdd(P.counter, 1ull);
+      if (itq >= total_items) { depth = -1; break; }
+      uint32_t sl = (uint32_t)(itq / npix);
+      uint32_t px = (uint32_t)(itq - (uint64_t)sl * npix);
+      sl += P.slice_begin;
+      st.x = sl << kItemShift | px;
+      // canonical slice k covers samples [floor(k*spp/S), floor((k+1)*spp/S)), S = RT_SLICES
+      st.y = (uint32_t)(((uint64_t)sl * P.spp) / RT_SLICES_DEV);
+      st.z = (uint32_t)(((uint64_t)(sl + 1) * P.spp) / RT_SLICES_DEV);
+      A = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+
+  if (depth >= 0) {
+    // ------------------------------------------------------------ the wave's random numbers
+    // stream: key = (pixel, sample), counter slot 0 = camera, k >= 1 = scatter at the k-th hit
+    const uint32_t px = st.x & kItemPixelMask;
+    const uint32_t hitno = P.max_depth - (uint32_t)depth + 1u;
+    const float4 xi = philox_uniforms(px, P.sample_offset + (regen ? st.y : st.y - 1u),
+                                      regen ? 0u : hitno, P.seed);
+    if (regen) {
+      // camera::get_ray (src/cpu/camera.h:28-35) with pixel jitter (main.cc:116-117)
+      const uint32_t row = px / P.width, ii = px - row * P.width;
+      const uint32_t j = P.height - 1 - row;
+      st.y += 1;
+      float u = ((float)ii + xi.x) * P.cam.inv_wm1;
+      float v = ((float)j + xi.y) * P.cam.inv_hm1;
+      float rad = P.cam.lens_radius * sqrtf(xi.z), sn, cs;
+      sincospif(2.0f * xi.w, &sn, &cs);
+      float rdx = rad * cs, rdy = rad * sn;
+      float offx = P.cam.u[0] * rdx + P.cam.v[0] * rdy;
+      float offy = P.cam.u[1] * rdx + P.cam.v[1] * rdy;
+      float offz = P.cam.u[2] * rdx + P.cam.v[2] * rdy;
+      RO.x = P.cam.origin[0] + offx;
+      RO.y = P.cam.origin[1] + offy;
+      RO.z = P.cam.origin[2] + offz;
+      float ddx = P.cam.llc_minus_origin[0] + u * P.cam.horizontal[0] + v * P.cam.vertical[0] - offx;
+      float ddy = P.cam.llc_minus_origin[1] + u * P.cam.horizontal[1] + v * P.cam.vertical[1] - offy;
+      float ddz = P.cam.llc_minus_origin[2] + u * P.cam.horizontal[2] + v * P.cam.vertical[2] - offz;
+      float len = sqrtf(ddx * ddx + ddy * ddy + ddz * ddz), inv = 1.0f / len;
+      RD.x = ddx * inv; RD.y = ddy * inv; RD.z = ddz * inv; RD.w = 0.f;
+      RO.w = len;
+      T.x = T.y = T.z = 1.0f;
+      depth = (int)P.max_depth;
+    } else {
+      // hit record, src/cpu/sphere.h:43-48 + hittable.h:16-19: point in f64, then narrowed
+      const float dx = RD.x, dy = RD.y, dz = RD.z;
+      const double4 S = exact[id];
       const float2 ax = aux[id];  // {1/r (signed), kind}
-      float onx = (float)(px - S.x) * ax.x, ony = (float)(py - S.y) * ax.x,
-            onz = (float)(pz - S.z) * ax.x;
+      float onx = (float)(hpx - S.x) * ax.x, ony = (float)(hpy - S.y) * ax.x,
+            onz = (float)(hpz - S.z) * ax.x;
       const bool front = (dx * onx + dy * ony + dz * onz) < 0.0f;
       const float nx = front ? onx : -onx, ny = front ? ony : -ony, nz = front ? onz : -onz;
-      RO.x = (float)px; RO.y = (float)py; RO.z = (float)pz;
-
-      const uint32_t slot = P.max_depth - (uint32_t)depth + 1u;  // k-th hit of this path
-      const float4 xi = philox_uniforms(st.x & kItemPixelMask, P.sample_offset + st.y - 1u, slot, P.seed);
+      RO.x = (float)hpx; RO.y = (float)hpy; RO.z = (float)hpz;
       const float4 M = mat[id];
       const uint32_t kind = (uint32_t)__float_as_int(ax.y);
+      const float dn = dx * nx + dy * ny + dz * nz;
       float sx, sy, sz;  // scattered direction (un-normalised, as in the reference)
       bool alive = true;
-      if (kind == 0u) {
-        // lambertian::scatter, src/cpu/material.h:19-32
+      if (kind != 2u) {
+        // lambertian::scatter (material.h:19-32) and metal::scatter (material.h:40-46) share the
+        // unit vector; the metal fuzz point is drawn INSIDE the unit ball
         float ux, uy, uz;
         unit_vector_from(xi.x, xi.y, ux, uy, uz);
-        sx = nx + ux; sy = ny + uy; sz = nz + uz;
-        if (fabsf(sx) < 1e-8f && fabsf(sy) < 1e-8f && fabsf(sz) < 1e-8f) { sx = nx; sy = ny; sz = nz; }
-        T.x *= M.x; T.y *= M.y; T.z *= M.z;
-      } else if (kind == 1u) {
-        // metal::scatter, src/cpu/material.h:40-46 (fuzz point drawn INSIDE the unit ball)
-        float dn = dx * nx + dy * ny + dz * nz;
-        sx = dx - 2.0f * dn * nx; sy = dy - 2.0f * dn * ny; sz = dz - 2.0f * dn * nz;
-        if (M.w > 0.0f) {
-          float ux, uy, uz;
-          unit_vector_from(xi.x, xi.y, ux, uy, uz);
-          float k = M.w * cbrtf(xi.z);
-          sx += k * ux; sy += k * uy; sz += k * uz;
+        if (kind == 0u) {
+          sx = nx + ux; sy = ny + uy; sz = nz + uz;
+          if (fabsf(sx) < 1e-8f && fabsf(sy) < 1e-8f && fabsf(sz) < 1e-8f) { sx = nx; sy = ny; sz = nz; }
+        } else {
+          sx = dx - 2.0f * dn * nx; sy = dy - 2.0f * dn * ny; sz = dz - 2.0f * dn * nz;
+          if (M.w > 0.0f) {
+            float k = M.w * cbrtf(xi.z);
+            sx += k * ux; sy += k * uy; sz += k * uz;
+          }
+          alive = (sx * nx + sy * ny + sz * nz) > 0.0f;
         }
-        alive = (sx * nx + sy * ny + sz * nz) > 0.0f;
         T.x *= M.x; T.y *= M.y; T.z *= M.z;
       } else {
         // dielectric::scatter + reflectance + refract, src/cpu/material.h:57-87, vec3.h:126-131
         float ratio = front ? (1.0f / M.w) : M.w;
-        float dn = dx * nx + dy * ny + dz * nz;
         float cos_t = fminf(-dn, 1.0f);
         float sin_t = sqrtf(fmaxf(0.0f, 1.0f - cos_t * cos_t));
         bool reflect_it = ratio * sin_t > 1.0f;
@@ -283,68 +338,21 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
         float len = sqrtf(sx * sx + sy * sy + sz * sz), inv = 1.0f / len;
         RD.x = sx * inv; RD.y = sy * inv; RD.z = sz * inv;
         RO.w = len;
+      } else {
+        RO.w = -1.0f;  // no ray this wave: the path regenerates in the next one
       }
     }
-  }
-
-  if (depth == 0) {
-    // ------------------------------------------------------------ regenerate the path
-    while (st.y == st.z) {  // item exhausted: flush it and fetch the next
-      if (st.x != 0xffffffffu) {
-        P.accum[(size_t)(st.x >> kItemShift) * npix + (st.x & kItemPixelMask)] = A;
-        st.x = 0xffffffffu;
-      }
-      unsigned long long itq = atomicAdd(P.counter, 1ull);
-      if (itq >= total_items) { depth = -1; break; }
-      uint32_t sl = (uint32_t)(itq / npix);
-      uint32_t px = (uint32_t)(itq - (uint64_t)sl * npix);
-      sl += P.slice_begin;
-      st.x = sl << kItemShift | px;
-      // canonical slice k covers samples [floor(k*spp/S), floor((k+1)*spp/S)), S = RT_SLICES
-      st.y = (uint32_t)(((uint64_t)sl * P.spp) / RT_SLICES_DEV);
-      st.z = (uint32_t)(((uint64_t)(sl + 1) * P.spp) / RT_SLICES_DEV);
-      A = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    if (depth == 0) {
-      // camera::get_ray (src/cpu/camera.h:28-35) with pixel jitter (main.cc:116-117)
-      const uint32_t px = st.x & kItemPixelMask;
-      const uint32_t row = px / P.width, ii = px - row * P.width;
-      const uint32_t j = P.height - 1 - row;
-      const float4 xi = philox_uniforms(px, P.sample_offset + st.y, 0u, P.seed);
-      st.y += 1;
-      float u = ((float)ii + xi.x) * P.cam.inv_wm1;
-      float v = ((float)j + xi.y) * P.cam.inv_hm1;
-      float rad = P.cam.lens_radius * sqrtf(xi.z), sn, cs;
-      sincospif(2.0f * xi.w, &sn, &cs);
-      float rdx = rad * cs, rdy = rad * sn;
-      float offx = P.cam.u[0] * rdx + P.cam.v[0] * rdy;
-      float offy = P.cam.u[1] * rdx + P.cam.v[1] * rdy;
-      float offz = P.cam.u[2] * rdx + P.cam.v[2] * rdy;
-      RO.x = P.cam.origin[0] + offx;
-      RO.y = P.cam.origin[1] + offy;
-      RO.z = P.cam.origin[2] + offz;
-      float ddx = P.cam.llc_minus_origin[0] + u * P.cam.horizontal[0] + v * P.cam.vertical[0] - offx;
-      float ddy = P.cam.llc_minus_origin[1] + u * P.cam.horizontal[1] + v * P.cam.vertical[1] - offy;
-      float ddz = P.cam.llc_minus_origin[2] + u * P.cam.horizontal[2] + v * P.cam.vertical[2] - offz;
-      float len = sqrtf(ddx * ddx + ddy * ddy + ddz * ddz), inv = 1.0f / len;
-      RD.x = ddx * inv; RD.y = ddy * inv; RD.z = ddz * inv; RD.w = 0.f;
-      RO.w = len;
-      T.x = T.y = T.z = 1.0f;
-      depth = (int)P.max_depth;
-    }
-  }
-
-  if (depth > 0) {
-    P.ray_o[i] = RO;
-    P.ray_d[i] = RD;
   } else {
-    P.ray_o[i] = make_float4(0.f, 0.f, 0.f, -1.0f);  // no ray: the filter skips the slot
+    RO.w = -1.0f;
   }
+
+  P.ray_o[i] = RO;
+  if (depth > 0) P.ray_d[i] = RD;
   T.w = __int_as_float(depth);
   P.thr[i] = T;
   P.acc[i] = A;
   P.it[i] = st;
-  return depth > 0 ? 1u : 0u;
+  return depth >= 0 ? 1u : 0u;  // still part of the frame (with or without a ray this wave)
 }
 
 // per-hit scene rows -> shared memory: 1-D bulk (TMA) copies completing on an mbarrier
