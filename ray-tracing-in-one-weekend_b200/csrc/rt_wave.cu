@@ -83,24 +83,28 @@ __device__ __forceinline__ void filter_rays(const WaveParams &P, const ConstRows
     uint32_t *const cand = P.cand_idx;
     const uint32_t nslots = P.n_slots;
     auto decide = [&](const float2 (&e)[G][NP], uint32_t s0) {
+      float mx[NP], my[NP];
       bool any = false;
 #pragma unroll
       for (int p = 0; p < NP; ++p) {
-        float mx = e[0][p].x, my = e[0][p].y;
+        mx[p] = e[0][p].x; my[p] = e[0][p].y;
 #pragma unroll
-        for (int k = 1; k < G; ++k) { mx = fmaxf(mx, e[k][p].x); my = fmaxf(my, e[k][p].y); }
-        any = any | (mx >= OOT[p].x) | (my >= OOT[p].y);  // no short-circuit: independent compares
+        for (int k = 1; k < G; ++k) { mx[p] = fmaxf(mx[p], e[k][p].x); my[p] = fmaxf(my[p], e[k][p].y); }
+        any = any | (mx[p] >= OOT[p].x) | (my[p] >= OOT[p].y);  // no short-circuit: independent compares
       }
       if (__any_sync(0xffffffffu, any)) {
+        // rare path, narrowed ray by ray: only a ray whose group maximum passed looks at its rows
 #pragma unroll
-        for (int k = 0; k < G; ++k)
+        for (int r = 0; r < R; ++r)
+          if (((r & 1) ? my[r >> 1] : mx[r >> 1]) >= WPK(OOT, r)) {
 #pragma unroll
-          for (int r = 0; r < R; ++r)
-            if (WPK(e[k], r) >= WPK(OOT, r)) {
-              if (cnt[r] < kCandPlanes) cand[off[r]] = s0 + k;
-              off[r] += nslots;
-              cnt[r] += 1;
-            }
+            for (int k = 0; k < G; ++k)
+              if (WPK(e[k], r) >= WPK(OOT, r)) {
+                if (cnt[r] < kCandPlanes) cand[off[r]] = s0 + k;
+                off[r] += nslots;
+                cnt[r] += 1;
+              }
+          }
       }
     };
 
