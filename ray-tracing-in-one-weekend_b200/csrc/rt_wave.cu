@@ -436,7 +436,13 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
     uint32_t live = 0;
 #pragma unroll 1
     for (int r = 0; r < R; ++r) live += shade_slot(P, base + r * stride, exact, mat, aux, npix, total_items);
+#ifdef RTW_CTA_SYNC
+    // CTA-wide barrier + vote: the warps of a CTA walk the sphere rows in step (one stream of
+    // constant-cache lines per CTA instead of one per warp)
+    if (!__syncthreads_or(live != 0u)) break;
+#else
     if (__all_sync(0xffffffffu, live == 0u)) break;  // warp-uniform exit keeps the loop convergent
+#endif
     filter_rays<R, G, CROWS>(P, CR, base, stride);
   }
 }
@@ -561,13 +567,24 @@ cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_c
 }
 
 template <int R, int G>
-static cudaError_t launch_fused_t(const WaveParams &p, const ConstRows &cr, bool crows, bool in_smem,
-                                  size_t smem, int grid, cudaStream_t st) {
+static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots, const ConstRows &cr,
+                                  bool crows, bool in_smem, size_t smem, int sm_count, int *grid_out,
+                                  cudaStream_t st) {
 #define RTW_FUSED(CR_, SM_)                                                                        \
   do {                                                                                             \
     auto k = fused_kernel<R, G, CR_, SM_>;                                                         \
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return e;                                                                \
+    int per_sm = 0;                                                                                \
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kWBlock, smem);                  \
+    if (e != cudaSuccess) return e;                                                                \
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;                                          \
+    /* persistent grid: every CTA must be resident (one full wave, a multiple of the SM count) */  \
+    const int grid = sm_count * (per_sm < RTW_MINB ? per_sm : RTW_MINB);                           \
+    const uint32_t n_slots = (uint32_t)grid * kWBlock * (uint32_t)R;                               \
+    if (n_slots > pool_slots) return cudaErrorInvalidValue;                                        \
+    wave_carve(p, pool, n_slots);                                                                  \
+    *grid_out = grid;                                                                              \
     k<<<grid, kWBlock, smem, st>>>(p, cr);                                                         \
   } while (0)
   if (crows && in_smem) RTW_FUSED(true, true);
@@ -587,15 +604,13 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
   int rpl = 2;
   if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
   if (rpl != 2 && rpl != 4) return cudaErrorInvalidValue;
-  const int grid = sm_count * RTW_MINB;
-  const uint32_t n_slots = (uint32_t)grid * kWBlock * (uint32_t)rpl;
-  if (n_slots > pool_slots) return cudaErrorInvalidValue;
-  wave_carve(p, pool, n_slots);
   const size_t scene_smem = (size_t)p.scene.n_pad * 56;
   const bool in_smem = (scene_smem + 1024) * RTW_MINB <= smem_optin_max;
   const size_t smem = in_smem ? scene_smem : 0;
-  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, cr, crows, in_smem, smem, grid, st)
-                           : launch_fused_t<2, 4>(p, cr, crows, in_smem, smem, grid, st);
+  int grid = 0;
+  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, pool, pool_slots, cr, crows, in_smem, smem, sm_count, &grid, st)
+                           : launch_fused_t<2, 4>(p, pool, pool_slots, cr, crows, in_smem, smem, sm_count, &grid, st);
+  const uint32_t n_slots = p.n_slots;
   if (info) {
     info->launches = 1; info->waves = 0; info->n_slots = n_slots; info->rays_per_lane = rpl;
     info->filter_grid = grid; info->shade_grid = 0; info->rows_in_constant_bank = crows;

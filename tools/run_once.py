@@ -26,9 +26,18 @@ def main():
     ap.add_argument("--reps", type=int, default=1)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--ppm", default=None)
+    ap.add_argument("--nspheres", type=int, default=0, help="truncate / tile the scene to n spheres (timing experiments)")
     a = ap.parse_args()
     rt = _load_pkg()
     rows = np.load(os.path.join(ROOT, "tests", "golden", f"{a.scene}_small.npz"))["spheres"]
+    if a.nspheres:
+        reps = -(-a.nspheres // len(rows))
+        tiles = []
+        for k in range(reps):
+            t = rows.copy()
+            t[1:, 2] += 30.0 * k  # shift copies along z (keep the ground in place)
+            tiles.append(t)
+        rows = np.concatenate(tiles)[:a.nspheres]
     if a.scene == "cover":
         cam = rt.Camera(aspect_ratio=a.w / a.h)
     else:
