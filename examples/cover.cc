@@ -3,7 +3,7 @@
 // depth 50), P3 image on stdout and a human log on stderr.  The pixel loops are one call into
 // the sm_100a kernels (rt::render); nothing is traced on the CPU.
 //
-//   ./rt_cover [--scene cover|three] [--width W] [--aspect 16:9] [--spp N] [--depth D]
+//   ./rt_cover [--scene cover|three|stress [--half H]] [--bvh] [--width W] [--aspect 16:9] [--spp N] [--depth D]
 //              [--seed S] [--out file.ppm] [--dump-scene file.f64] > image.ppm
 #include <chrono>
 #include <cstdlib>
@@ -20,6 +20,8 @@ int main(int argc, char **argv) {
   double aspect_ratio = 3.0 / 2.0;
   int image_width = 1200, samples_per_pixel = 500, max_depth = 50;
   unsigned long long seed = 0;
+  int half = 158;
+  bool use_bvh = false;
   for (int k = 1; k < argc; ++k) {
     std::string a = argv[k];
     auto val = [&]() -> const char * {
@@ -37,13 +39,16 @@ int main(int argc, char **argv) {
     else if (a == "--depth") max_depth = std::atoi(val());
     else if (a == "--seed") seed = std::strtoull(val(), nullptr, 10);
     else if (a == "--out") out = val();
+    else if (a == "--half") half = std::atoi(val());
+    else if (a == "--bvh") use_bvh = true;
     else if (a == "--dump-scene") dump = val();
     else { std::cerr << "unknown option " << a << "\n"; return 2; }
   }
   const int image_height = static_cast<int>(image_width / aspect_ratio);
 
   // World
-  hittable_list world = scene == "three" ? three_sphere_scene() : random_scene();
+  hittable_list world = scene == "three" ? three_sphere_scene()
+                        : scene == "stress" ? stress_scene(half) : random_scene();
   if (!dump.empty()) {  // f64 [n][9]: cx cy cz radius kind r g b fuzz|ir (the oracle's dump layout)
     FILE *f = std::fopen(dump.c_str(), "wb");
     if (!f) { std::perror(dump.c_str()); return 2; }
@@ -72,7 +77,7 @@ int main(int argc, char **argv) {
             << "Spheres: " << world.objects.size() << "\n";
   try {
     auto t0 = std::chrono::high_resolution_clock::now();
-    image img = render(world, cam, image_width, image_height, samples_per_pixel, max_depth, seed);
+    image img = render(world, cam, image_width, image_height, samples_per_pixel, max_depth, seed, 0, use_bvh);
     auto t1 = std::chrono::high_resolution_clock::now();
     img.write_ppm(out.c_str());
     double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();

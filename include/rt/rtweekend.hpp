@@ -212,12 +212,15 @@ class camera {
 // Book-cover scene: ground + 22x22 grid of small spheres (kept when farther than 0.9 from
 // (4, 0.2, 0)) + three big ones.  Draw order per grid cell: material choice, centre z-jitter,
 // centre x-jitter, then material parameters (lambertian: right factor before left factor).
-inline hittable_list random_scene(scene_rng &rng) {
+// `half` = half-width of the grid of small spheres: 11 is the book cover (22 x 22 cells, 486
+// spheres with the default seed); 158 gives the ~100 k-sphere stress scene of BASELINE.json
+// configs[3] (same recipe, same draw order, larger grid).
+inline hittable_list random_scene(scene_rng &rng, int half = 11) {
   hittable_list world;
   world.add(make_shared<sphere>(point3(0, -1000, 0), 1000, make_shared<lambertian>(color(0.5, 0.5, 0.5))));
   const point3 keep_clear(4, 0.2, 0);
-  for (int a = -11; a < 11; ++a)
-    for (int b = -11; b < 11; ++b) {
+  for (int a = -half; a < half; ++a)
+    for (int b = -half; b < half; ++b) {
       const double pick = rng.random_double();
       const double jz = rng.random_double(), jx = rng.random_double();
       const point3 c(a + 0.9 * jx, 0.2, b + 0.9 * jz);
@@ -242,6 +245,10 @@ inline hittable_list random_scene(scene_rng &rng) {
 inline hittable_list random_scene() {
   scene_rng rng;
   return random_scene(rng);
+}
+inline hittable_list stress_scene(int half = 158, uint32_t seed = 1u) {
+  scene_rng rng(seed);
+  return random_scene(rng, half);
 }
 
 // Three spheres on a ground ball with a hollow glass bubble (archive/listing69/main.cc:43-71).
@@ -276,7 +283,7 @@ struct image {
 // The pixel/sample loops of main() (src/cpu/main.cc:111-123) as one call.
 inline image render(const hittable_list &world, const camera &cam, uint32_t image_width,
                     uint32_t image_height, uint32_t samples_per_pixel, uint32_t max_depth,
-                    uint64_t seed = 0, int device = 0) {
+                    uint64_t seed = 0, int device = 0, bool use_bvh = false) {
   std::vector<rt_sphere> flat = world.flatten();
   rt_scene *sc = nullptr;
   check(rt_scene_create(flat.data(), (uint32_t)flat.size(), device, &sc));
@@ -284,6 +291,7 @@ inline image render(const hittable_list &world, const camera &cam, uint32_t imag
   cfg.width = image_width; cfg.height = image_height;
   cfg.samples_per_pixel = samples_per_pixel; cfg.max_depth = max_depth;
   cfg.seed = seed; cfg.slice_begin = 0; cfg.slice_end = RT_SLICES; cfg.device = device;
+  cfg.flags = use_bvh ? RT_FLAG_BVH : 0u;
   image img;
   img.width = image_width; img.height = image_height;
   img.rgb.resize((size_t)image_width * image_height * 3);

@@ -41,6 +41,9 @@ struct rt_scene {
   float2 *aux;
   uint32_t n_pad;
   std::vector<float4> host_fast;  // host copy of the filter rows (kernel-parameter path)
+  BvhNode *bvh_nodes;             // optional hierarchy, built on the host at scene creation
+  uint32_t *bvh_prim;
+  uint32_t bvh_node_count;
 };
 
 struct rt_frame {
@@ -132,6 +135,21 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
   CU(cudaMemcpy(sc->mat, mat.data(), m * sizeof(float4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(sc->aux, aux.data(), m * sizeof(float2), cudaMemcpyHostToDevice));
   sc->host_fast = fast;
+  {
+    // the north-star's optional BVH: built here on the host, used when a render asks for it
+    std::vector<BvhNode> nodes;
+    std::vector<uint32_t> prim;
+    build_bvh(exact.data(), n, nodes, prim);
+    if (prim.empty()) prim.push_back(0);
+    sc->bvh_node_count = (uint32_t)nodes.size();
+    if ((e = cudaMalloc(&sc->bvh_nodes, nodes.size() * sizeof(BvhNode))) != cudaSuccess ||
+        (e = cudaMalloc(&sc->bvh_prim, prim.size() * sizeof(uint32_t))) != cudaSuccess) {
+      rt_scene_destroy(sc);
+      return fail(RT_E_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
+    }
+    CU(cudaMemcpy(sc->bvh_nodes, nodes.data(), nodes.size() * sizeof(BvhNode), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(sc->bvh_prim, prim.data(), prim.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  }
   *out = sc;
   return RT_OK;
 }
@@ -140,6 +158,7 @@ extern "C" int rt_scene_destroy(rt_scene *sc) {
   if (!sc) return RT_OK;
   cudaSetDevice(sc->device);
   cudaFree(sc->fast); cudaFree(sc->exact); cudaFree(sc->mat); cudaFree(sc->aux);
+  cudaFree(sc->bvh_nodes); cudaFree(sc->bvh_prim);
   delete sc;
   return RT_OK;
 }
@@ -153,6 +172,7 @@ extern "C" int rt_scene_count(const rt_scene *sc, uint32_t *n) {
 static SceneView view_of(const rt_scene *sc) {
   SceneView v;
   v.fast = sc->fast; v.exact = sc->exact; v.mat = sc->mat; v.aux = sc->aux; v.n = sc->n; v.n_pad = sc->n_pad;
+  v.bvh_nodes = sc->bvh_nodes; v.bvh_prim = sc->bvh_prim;
   return v;
 }
 
@@ -344,8 +364,8 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
       wave_carve(w, f->pool, f->pool_slots);
       CU(run_wavefront(w, sc->host_fast.data(), f->sm_count, f->smem_optin, f->stream, f->host_live, &info));
     } else {
-      CU(run_fused(w, f->pool, f->pool_slots, sc->host_fast.data(), f->sm_count, f->smem_optin,
-                   f->stream, &info));
+      CU(run_fused(w, f->pool, f->pool_slots, sc->host_fast.data(), (cfg->flags & RT_FLAG_BVH) != 0,
+                   f->sm_count, f->smem_optin, f->stream, &info));
     }
     launches = info.launches;
   }

@@ -14,10 +14,20 @@ struct SceneView {
   const double4 *exact;  // [n_pad] {cx, cy, cz, signed radius}       f64 candidate resolution
   const float4 *mat;     // [n] {albedo.r, albedo.g, albedo.b, fuzz | ir}
   const float2 *aux;     // [n] {1 / signed radius, material kind (integer bits)}
+  const struct BvhNode *bvh_nodes;  // optional hierarchy (rt_bvh.cu); root = node 0
+  const uint32_t *bvh_prim;         // sphere indices referenced by the leaves
   uint32_t n;            // spheres in the hittable_list
   uint32_t n_pad;        // rows allocated: n rounded up to a multiple of kRowPad; padding rows can
                          // never pass the filter (w = -inf)
 };
+
+// One node of the optional BVH, 32 bytes.  count > 0: leaf over bvh_prim[first, first+count);
+// count == 0: inner node with children first and first + 1.  Bounds are f32, rounded outwards.
+struct BvhNode {
+  float lo[3], hi[3];
+  uint32_t first, count;
+};
+constexpr unsigned kBvhLeafMax = 4, kBvhMaxDepth = 64;
 
 // camera (src/cpu/camera.h:8-26) derived on the host in f64, narrowed once.
 struct CameraF32 {

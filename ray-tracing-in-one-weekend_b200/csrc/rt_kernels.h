@@ -6,6 +6,8 @@
 
 #include "rt_device.cuh"
 
+#include <vector>
+
 #define RT_SLICES_DEV 64u  // == RT_SLICES (include/rt_b200.h)
 // work item = slice << kItemShift | pixel (0xffffffff = none)
 constexpr unsigned kItemShift = 26;
@@ -82,9 +84,15 @@ cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_c
                           size_t smem_optin_max, cudaStream_t st, unsigned int *host_live,
                           WaveRunInfo *info);
 
+// Host-side BVH build over {cx, cy, cz, signed r} (rt_bvh.cu).
+void build_bvh(const double4 *spheres, uint32_t n, std::vector<BvhNode> &nodes,
+               std::vector<uint32_t> &prim);
+
 // Fused persistent form: one launch per frame; carves n_slots = grid * block * R out of the pool.
+// use_bvh: closest hit by BVH traversal (scene.bvh_nodes) instead of the brute-force filter.
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
-                      int sm_count, size_t smem_optin_max, cudaStream_t st, WaveRunInfo *info);
+                      bool use_bvh, int sm_count, size_t smem_optin_max, cudaStream_t st,
+                      WaveRunInfo *info);
 
 // rays_per_lane: 1, 2 or 4 (0 = default).  Launches the persistent path kernel.
 // host_rows: host copy of scene.fast (n_pad + 4 rows) or nullptr.

@@ -184,6 +184,7 @@ __device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, d
 // a new path (miss / empty slot) or the scatter sample of the hit.  (3) camera::get_ray or
 // material::scatter.  A path that ends at a hit (absorbed, bounce limit) leaves the slot without a
 // ray for one wave and regenerates in the next one.  Returns 0 once the slot is retired.
+template <bool BVH>
 __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32_t i,
                                                const double4 *exact, const float4 *mat,
                                                const float2 *aux, const uint32_t npix,
@@ -207,15 +208,22 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
     ray.a = ray.dx * ray.dx + ray.dy * ray.dy + ray.dz * ray.dz;
     ray.tminA = 0.001 * (double)RO.w * ray.a;  // main.cc:19 t_min in unit-direction units, times a
     double bestN = __longlong_as_double(0x7ff0000000000000ll);
-    const uint32_t cnt = P.cand_cnt[i];
-    if (cnt <= kCandPlanes) {
-      for (uint32_t k = 0; k < cnt; ++k) {
-        const uint32_t s = P.cand_idx[(size_t)k * P.n_slots + i];
-        if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+    if (BVH) {
+      // the traversal already resolved the closest hit: {id, numerator of the root}
+      id = (int)P.cand_idx[i];
+      bestN = __hiloint2double((int)P.cand_idx[(size_t)2 * P.n_slots + i],
+                               (int)P.cand_idx[(size_t)1 * P.n_slots + i]);
+    } else {
+      const uint32_t cnt = P.cand_cnt[i];
+      if (cnt <= kCandPlanes) {
+        for (uint32_t k = 0; k < cnt; ++k) {
+          const uint32_t s = P.cand_idx[(size_t)k * P.n_slots + i];
+          if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+        }
+      } else {  // candidate planes overflowed: exact test of every sphere (rare)
+        for (uint32_t s = 0; s < P.scene.n; ++s)
+          if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
       }
-    } else {  // candidate planes overflowed: exact test of every sphere (rare)
-      for (uint32_t s = 0; s < P.scene.n; ++s)
-        if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
     }
     if (id < 0) {
       // sky, src/cpu/main.cc:27-29 (direction already unit length)
@@ -400,11 +408,117 @@ shade_kernel(const __grid_constant__ WaveParams P) {
   const uint64_t total_items = (uint64_t)npix * (P.slice_end - P.slice_begin);
   uint32_t live_lanes = 0;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_slots; i += gridDim.x * blockDim.x)
-    live_lanes += shade_slot(P, i, exact, mat, aux, npix, total_items);
+    live_lanes += shade_slot<false>(P, i, exact, mat, aux, npix, total_items);
   // live rays of the next wave (the host stops the frame when this stays 0)
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) live_lanes += __shfl_xor_sync(0xffffffffu, live_lanes, o);
   if ((threadIdx.x & 31) == 0 && live_lanes) atomicAdd(P.live, live_lanes);
+}
+
+// ================================================================ BVH traversal (optional mode)
+// Closest hit of R rays through the host-built hierarchy (rt_bvh.cu) with the REFERENCE's result:
+// the linear scan of hittable_list::hit accepts sphere s when its root N_s (near root if >= t_min,
+// else far root) is <= the best so far, so the winner is the smallest root and, among equal roots,
+// the LARGEST index (sphere.h:38-40 + hittable_list.h:34-39).  That rule does not depend on the
+// visiting order, so leaves may be visited in any order.  Boxes are tested in f32 with outward
+// slack; a node is skipped only if it lies entirely beyond the best root or before t_min.
+// Writes {id, root numerator} to candidate planes 0..2 of the slot.
+template <int R>
+__device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *exact, const uint32_t base,
+                                          const uint32_t stride) {
+  const BvhNode *nodes = P.scene.bvh_nodes;
+  const uint32_t *prim = P.scene.bvh_prim;
+  const float4 *fast = P.scene.fast;
+#pragma unroll 1
+  for (int r = 0; r < R; ++r) {
+    const uint32_t slot = base + r * stride;
+    const float4 o = P.ray_o[slot];
+    if (!(o.w > 0.0f)) continue;  // no ray this wave
+    const float4 d = P.ray_d[slot];
+    WRay ray;
+    ray.ox = o.x; ray.oy = o.y; ray.oz = o.z; ray.dx = d.x; ray.dy = d.y; ray.dz = d.z;
+    ray.a = ray.dx * ray.dx + ray.dy * ray.dy + ray.dz * ray.dz;
+    ray.tminA = 0.001 * (double)o.w * ray.a;
+    double bestN = __longlong_as_double(0x7ff0000000000000ll);
+    int id = -1;
+    const float tmin_f = 0.001f * o.w * 0.9999f;
+    float tbest = __int_as_float(0x7f800000);  // upper bound of the best root (unit-direction t)
+    const float ix = 1.0f / (fabsf(d.x) > 1e-30f ? d.x : copysignf(1e-30f, d.x));
+    const float iy = 1.0f / (fabsf(d.y) > 1e-30f ? d.y : copysignf(1e-30f, d.y));
+    const float iz = 1.0f / (fabsf(d.z) > 1e-30f ? d.z : copysignf(1e-30f, d.z));
+    const float nod = -(o.x * d.x + o.y * d.y + o.z * d.z);
+    const float ox2 = 2.0f * o.x, oy2 = 2.0f * o.y, oz2 = 2.0f * o.z;
+    const float oot = (o.x * o.x + o.y * o.y + o.z * o.z) * (1.0f - RTB_FILTER_SLACK);
+    // entry distance of the ray into a node's box, or +inf when the box can be skipped
+    auto entry = [&](const float4 a, const float4 b) {  // a = {lo.xyz, hi.x}, b = {hi.yz, first, count}
+      float t0 = (a.x - o.x) * ix, t1 = (a.w - o.x) * ix;
+      float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
+      t0 = (a.y - o.y) * iy; t1 = (b.x - o.y) * iy;
+      tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
+      t0 = (a.z - o.z) * iz; t1 = (b.y - o.z) * iz;
+      tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
+      tf = tf * 1.00001f + 1e-6f;  // robust: never lose a box to rounding
+      const bool hit = tn <= tf && tf >= tmin_f && tn <= tbest;
+      return hit ? tn : __int_as_float(0x7f800000);
+    };
+    uint32_t stack[kBvhMaxDepth];
+    int sp = 0;
+    uint32_t node = 0;
+    {
+      const float4 *q = reinterpret_cast<const float4 *>(nodes);
+      if (entry(__ldg(q), __ldg(q + 1)) == __int_as_float(0x7f800000)) node = 0xffffffffu;
+    }
+    while (node != 0xffffffffu) {
+      const float4 *q = reinterpret_cast<const float4 *>(nodes + node);
+      const float4 nb = __ldg(q + 1);
+      const uint32_t first = (uint32_t)__float_as_int(nb.z), count = (uint32_t)__float_as_int(nb.w);
+      if (count) {
+        for (uint32_t k = 0; k < count; ++k) {
+          const uint32_t s = __ldg(prim + first + k);
+          const float4 S = __ldg(fast + s);
+          const float b = fmaf(S.x, d.x, fmaf(S.y, d.y, fmaf(S.z, d.z, nod)));
+          const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
+          if (e >= oot) {
+            const double4 E = exact[s];
+            double ocx = ray.ox - E.x, ocy = ray.oy - E.y, ocz = ray.oz - E.z;
+            double half_b = ocx * ray.dx + ocy * ray.dy + ocz * ray.dz;
+            double c = ocx * ocx + ocy * ocy + ocz * ocz - E.w * E.w;
+            double disc = half_b * half_b - ray.a * c;
+            if (disc >= 0.0) {
+              double sq = wave_dsqrt(disc);
+              double N = -half_b - sq;
+              if (N < ray.tminA) N = -half_b + sq;
+              if (N >= ray.tminA && (N < bestN || (N == bestN && (int)s > id))) {
+                bestN = N; id = (int)s;
+                tbest = (float)(N * 1.00001) + 1e-6f;
+              }
+            }
+          }
+        }
+        node = sp ? stack[--sp] : 0xffffffffu;
+      } else {
+        // inner node: test both children, descend into the nearer one first
+        const float4 *c0 = reinterpret_cast<const float4 *>(nodes + first);
+        const float t0 = entry(__ldg(c0), __ldg(c0 + 1));
+        const float t1 = entry(__ldg(c0 + 2), __ldg(c0 + 3));
+        const float INF = __int_as_float(0x7f800000);
+        if (t0 == INF && t1 == INF) {
+          node = sp ? stack[--sp] : 0xffffffffu;
+        } else if (t1 == INF) {
+          node = first;
+        } else if (t0 == INF) {
+          node = first + 1;
+        } else {
+          const bool near0 = t0 <= t1;
+          stack[sp++] = near0 ? first + 1 : first;
+          node = near0 ? first : first + 1;
+        }
+      }
+    }
+    P.cand_idx[slot] = (uint32_t)id;
+    P.cand_idx[(size_t)1 * P.n_slots + slot] = (uint32_t)__double2loint(bestN);
+    P.cand_idx[(size_t)2 * P.n_slots + slot] = (uint32_t)__double2hiint(bestN);
+  }
 }
 
 // ================================================================ fused persistent form
@@ -412,7 +526,7 @@ shade_kernel(const __grid_constant__ WaveParams P) {
 // loop, state in the pool) and filter (R rays at once, registers hold nothing but rays).  No
 // kernel boundary, no inter-lane dependency; warps of an SM drift apart, so the latency-bound
 // shade phases of some warps overlap the FMA-pipe-bound filter phases of the others.
-template <int R, int G, bool CROWS, bool SMEM>
+template <int R, int G, bool CROWS, bool SMEM, bool BVH>
 __global__ void __launch_bounds__(kWBlock, RTW_MINB)
 fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -435,7 +549,7 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
   for (;;) {
     uint32_t live = 0;
 #pragma unroll 1
-    for (int r = 0; r < R; ++r) live += shade_slot(P, base + r * stride, exact, mat, aux, npix, total_items);
+    for (int r = 0; r < R; ++r) live += shade_slot<BVH>(P, base + r * stride, exact, mat, aux, npix, total_items);
 #ifdef RTW_CTA_SYNC
     // CTA-wide barrier + vote: the warps of a CTA walk the sphere rows in step (one stream of
     // constant-cache lines per CTA instead of one per warp)
@@ -443,7 +557,8 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
 #else
     if (__all_sync(0xffffffffu, live == 0u)) break;  // warp-uniform exit keeps the loop convergent
 #endif
-    filter_rays<R, G, CROWS>(P, CR, base, stride);
+    if (BVH) bvh_trace<R>(P, exact, base, stride);
+    else filter_rays<R, G, CROWS>(P, CR, base, stride);
   }
 }
 
@@ -568,11 +683,11 @@ cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_c
 
 template <int R, int G>
 static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots, const ConstRows &cr,
-                                  bool crows, bool in_smem, size_t smem, int sm_count, int *grid_out,
-                                  cudaStream_t st) {
-#define RTW_FUSED(CR_, SM_)                                                                        \
+                                  bool crows, bool in_smem, bool bvh, size_t smem, int sm_count,
+                                  int *grid_out, cudaStream_t st) {
+#define RTW_FUSED(CR_, SM_, BV_)                                                                   \
   do {                                                                                             \
-    auto k = fused_kernel<R, G, CR_, SM_>;                                                         \
+    auto k = fused_kernel<R, G, CR_, SM_, BV_>;                                                         \
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return e;                                                                \
     int per_sm = 0;                                                                                \
@@ -587,16 +702,20 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
     *grid_out = grid;                                                                              \
     k<<<grid, kWBlock, smem, st>>>(p, cr);                                                         \
   } while (0)
-  if (crows && in_smem) RTW_FUSED(true, true);
-  else if (crows) RTW_FUSED(true, false);
-  else if (in_smem) RTW_FUSED(false, true);
-  else RTW_FUSED(false, false);
+  if (bvh && in_smem) RTW_FUSED(false, true, true);
+  else if (bvh) RTW_FUSED(false, false, true);
+  else if (crows && in_smem) RTW_FUSED(true, true, false);
+  else if (crows) RTW_FUSED(true, false, false);
+  else if (in_smem) RTW_FUSED(false, true, false);
+  else RTW_FUSED(false, false, false);
 #undef RTW_FUSED
   return cudaGetLastError();
 }
 
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
-                      int sm_count, size_t smem_optin_max, cudaStream_t st, WaveRunInfo *info) {
+                      bool use_bvh, int sm_count, size_t smem_optin_max, cudaStream_t st,
+                      WaveRunInfo *info) {
+  if (use_bvh && !p.scene.bvh_nodes) return cudaErrorInvalidValue;
   static ConstRows cr;
   const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
                      !getenv("RT_B200_NO_CONST_ROWS");
@@ -608,8 +727,8 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
   const bool in_smem = (scene_smem + 1024) * RTW_MINB <= smem_optin_max;
   const size_t smem = in_smem ? scene_smem : 0;
   int grid = 0;
-  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, pool, pool_slots, cr, crows, in_smem, smem, sm_count, &grid, st)
-                           : launch_fused_t<2, 4>(p, pool, pool_slots, cr, crows, in_smem, smem, sm_count, &grid, st);
+  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, smem, sm_count, &grid, st)
+                           : launch_fused_t<2, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, smem, sm_count, &grid, st);
   const uint32_t n_slots = p.n_slots;
   if (info) {
     info->launches = 1; info->waves = 0; info->n_slots = n_slots; info->rays_per_lane = rpl;

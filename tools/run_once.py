@@ -26,10 +26,14 @@ def main():
     ap.add_argument("--reps", type=int, default=1)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--ppm", default=None)
+    ap.add_argument("--bvh", action="store_true", help="closest hit through the host-built BVH")
+    ap.add_argument("--rows", default=None, help="scene dump file (f64 [n][9]) instead of a golden scene")
     ap.add_argument("--nspheres", type=int, default=0, help="truncate / tile the scene to n spheres (timing experiments)")
     a = ap.parse_args()
     rt = _load_pkg()
     rows = np.load(os.path.join(ROOT, "tests", "golden", f"{a.scene}_small.npz"))["spheres"]
+    if a.rows:
+        rows = np.fromfile(a.rows, np.float64).reshape(-1, 9)
     if a.nspheres:
         reps = -(-a.nspheres // len(rows))
         tiles = []
@@ -45,7 +49,7 @@ def main():
                         float(np.sqrt(27.0)))
     scene = rt.Scene(rows)
     frame = rt.Frame(a.w, a.h)
-    cfg = rt.Config(a.w, a.h, a.spp, a.depth, seed=a.seed)
+    cfg = rt.Config(a.w, a.h, a.spp, a.depth, seed=a.seed, flags=rt.FLAG_BVH if a.bvh else 0)
     for _ in range(a.reps):
         st = frame.render(scene, cam, cfg)
         frame.reduce_local(cfg)
