@@ -65,8 +65,7 @@ typedef struct rt_config {
 } rt_config;
 
 #define RT_FLAG_COUNT_RAYS 1u /* fill rt_stats.rays (one atomic per work item) */
-#define RT_FLAG_MEGAKERNEL 2u /* register-resident megakernel (rt_path.cu) instead of the fused kernel */
-#define RT_FLAG_WAVEFRONT 4u  /* two-kernel shade/filter wavefront (rt_wave.cu) */
+#define RT_FLAG_WAVEFRONT 4u  /* two-kernel shade/filter wavefront instead of the fused persistent kernel */
 #define RT_FLAG_BVH 8u        /* closest hit through the host-built BVH instead of the brute-force scan
                                  over the reference's sphere order (same hit, same image) */
 

@@ -20,7 +20,7 @@ LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
 SLICES = 64
 FLAG_COUNT_RAYS = 1
-FLAG_MEGAKERNEL, FLAG_WAVEFRONT, FLAG_BVH = 2, 4, 8
+FLAG_WAVEFRONT, FLAG_BVH = 4, 8
 
 
 class RtError(RuntimeError):

@@ -303,11 +303,10 @@ static int check_cfg(const rt_config *cfg, const rt_frame *f) {
 }
 
 // ---------------------------------------------------------------- the hot path
-// 0 = fused persistent kernel (default), 1 = register-resident megakernel, 2 = two-kernel wavefront
+// 0 = fused persistent kernel (default), 2 = two-kernel wavefront (A/B variant of the same code)
 static int render_mode(const rt_config *cfg) {
-  if (const char *e = getenv("RT_B200_MODE"))
-    return strcmp(e, "mega") == 0 ? 1 : strcmp(e, "wave") == 0 ? 2 : 0;
-  return (cfg->flags & RT_FLAG_MEGAKERNEL) ? 1 : (cfg->flags & RT_FLAG_WAVEFRONT) ? 2 : 0;
+  if (const char *e = getenv("RT_B200_MODE")) return strcmp(e, "wave") == 0 ? 2 : 0;
+  return (cfg->flags & RT_FLAG_WAVEFRONT) ? 2 : 0;
 }
 
 extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_config *cfg,
@@ -319,14 +318,14 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
   CU(cudaSetDevice(f->device));
   CamFrame cf;
   derive_camera(cam, &cf);
-  PathParams p;
-  p.scene = view_of(sc);
-  p.cam = narrow_camera(cf, f->w, f->h);
-  p.width = f->w; p.height = f->h;
-  p.spp = cfg->samples_per_pixel; p.max_depth = cfg->max_depth;
-  p.seed = cfg->seed; p.sample_offset = cfg->sample_offset;
-  p.slice_begin = cfg->slice_begin; p.slice_end = cfg->slice_end;
-  p.accum = f->accum; p.counter = f->counters;
+  WaveParams w;
+  w.scene = view_of(sc);
+  w.cam = narrow_camera(cf, f->w, f->h);
+  w.width = f->w; w.height = f->h;
+  w.spp = cfg->samples_per_pixel; w.max_depth = cfg->max_depth;
+  w.seed = cfg->seed; w.sample_offset = cfg->sample_offset;
+  w.slice_begin = cfg->slice_begin; w.slice_end = cfg->slice_end;
+  w.accum = f->accum; w.counter = f->counters;
   f->last_n = sc->n;
 
   uint32_t launches = 0;
@@ -337,14 +336,8 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
     CU(cudaMemsetAsync(f->accum + (size_t)cfg->slice_begin * f->npix, 0,
                        (size_t)(cfg->slice_end - cfg->slice_begin) * f->npix * sizeof(float4),
                        f->stream));
-  } else if (render_mode(cfg) == 1) {
-    int rpl = 0;
-    if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
-    PathLaunchInfo info;
-    CU(launch_path(p, sc->host_fast.data(), rpl, f->sm_count, f->smem_optin, f->stream, &info));
-    launches = 1;
   } else {
-    // wavefront: shade / filter kernels alternating over a pool of path slots
+    // path slots live in a pool in device memory (allocated on first use)
     if (!f->pool) {
       uint32_t slots = wave_default_slots(f->sm_count);
       if (const char *e = getenv("RT_B200_WAVE_SLOTS")) slots = (uint32_t)atol(e) / 1024u * 1024u;
@@ -354,11 +347,7 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
       CU(cudaMallocHost(&f->host_live, sizeof(unsigned int)));
       f->pool_slots = slots;
     }
-    WaveParams w;
-    w.scene = p.scene; w.cam = p.cam; w.width = p.width; w.height = p.height;
-    w.spp = p.spp; w.max_depth = p.max_depth; w.seed = p.seed; w.sample_offset = p.sample_offset;
-    w.slice_begin = p.slice_begin; w.slice_end = p.slice_end;
-    w.accum = p.accum; w.counter = p.counter; w.live = f->live;
+    w.live = f->live;
     WaveRunInfo info;
     if (render_mode(cfg) == 2) {
       wave_carve(w, f->pool, f->pool_slots);

@@ -19,24 +19,6 @@ constexpr unsigned kRowPad = 8, kRowTail = 8;
 
 namespace rtb {
 
-struct PathParams {
-  SceneView scene;
-  CameraF32 cam;
-  uint32_t width, height;
-  uint32_t spp, max_depth;
-  uint64_t seed;
-  uint32_t sample_offset;
-  uint32_t slice_begin, slice_end;
-  float4 *accum;                 // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
-  unsigned long long *counter;   // work-queue head (zeroed before launch)
-};
-
-struct PathLaunchInfo {
-  int rays_per_lane, grid, block, blocks_per_sm;
-  size_t smem_bytes;
-  bool scene_in_smem, rows_in_constant_bank;
-};
-
 // Filter rows passed by value as a kernel parameter (constant bank 0): scenes of up to
 // kConstRows - 4 padded rows.  16 KB of the 32 KB parameter space.
 constexpr int kConstRows = 1024;
@@ -93,12 +75,6 @@ void build_bvh(const double4 *spheres, uint32_t n, std::vector<BvhNode> &nodes,
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
                       bool use_bvh, int sm_count, size_t smem_optin_max, cudaStream_t st,
                       WaveRunInfo *info);
-
-// rays_per_lane: 1, 2 or 4 (0 = default).  Launches the persistent path kernel.
-// host_rows: host copy of scene.fast (n_pad + 4 rows) or nullptr.
-cudaError_t launch_path(const PathParams &p, const float4 *host_rows, int rays_per_lane,
-                        int sm_count, size_t smem_optin_max, cudaStream_t st,
-                        PathLaunchInfo *info);
 
 // dst[i] = canonical sub-tree sum of slices [slice_begin, slice_end) (aligned power of 2).
 cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t slice_begin,

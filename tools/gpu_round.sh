@@ -3,7 +3,7 @@
 TAG=${1:-r01}
 O=gpurun_out; mkdir -p $O
 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O/${TAG}_pytest_gpu.log; tail -3 $O/${TAG}_pytest_gpu.log
-for M in mega wave; do RT_B200_MODE=$M python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -1 | sed "s/^/mode $M: /"; done | tee $O/${TAG}_pytest_modes.log
+for M in wave; do RT_B200_MODE=$M python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -1 | sed "s/^/mode $M: /"; done | tee $O/${TAG}_pytest_modes.log
 python bench.py --impl reference --steps 1 --warmup 1 > $O/${TAG}_bench_ref.json 2> $O/${TAG}_bench.err; cut -c1-300 $O/${TAG}_bench_ref.json
 python bench.py > $O/${TAG}_bench.json 2>> $O/${TAG}_bench.err; echo "bench rc=$?"; cut -c1-400 $O/${TAG}_bench.json
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
