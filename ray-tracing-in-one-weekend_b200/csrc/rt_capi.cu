@@ -64,6 +64,11 @@ struct rt_frame {
   uint32_t pool_slots;
   unsigned int *live;       // device counter
   unsigned int *host_live;  // pinned
+  // hand-out order of the next frame: pixels by descending cost of the frame rendered before
+  uint32_t *order, *sort_keys, *sort_keys_out, *sort_iota, *heavy;
+  void *sort_temp;
+  size_t sort_temp_bytes;
+  bool order_valid;
 };
 
 extern "C" const char *rt_last_error(void) { return g_err; }
@@ -266,6 +271,8 @@ extern "C" int rt_frame_destroy(rt_frame *f) {
   cudaFree(f->accum); cudaFree(f->partial); cudaFree(f->rgb_words); cudaFree(f->linear);
   cudaFree(f->counters);
   cudaFree(f->pool); cudaFree(f->live);
+  cudaFree(f->order); cudaFree(f->sort_keys); cudaFree(f->sort_keys_out); cudaFree(f->sort_iota);
+  cudaFree(f->sort_temp); cudaFree(f->heavy);
   if (f->host_live) cudaFreeHost(f->host_live);
   for (int k = 0; k < 4; ++k)
     if (f->ev[k]) cudaEventDestroy(f->ev[k]);
@@ -326,7 +333,17 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
   w.seed = cfg->seed; w.sample_offset = cfg->sample_offset;
   w.slice_begin = cfg->slice_begin; w.slice_end = cfg->slice_end;
   w.accum = f->accum; w.counter = f->counters;
+  w.order = f->order_valid && !getenv("RT_B200_NO_COST_ORDER") ? f->order : nullptr;
+  w.heavy = f->heavy;
   f->last_n = sc->n;
+  // hand-out order = largest slices first; trailing slices without samples are not queued
+  const uint32_t n_own = cfg->slice_end - cfg->slice_begin;
+  w.n_orders = 0;
+  for (uint32_t ord = 0; ord < n_own; ++ord) {
+    uint32_t a, b;
+    slice_range(slice_in_order(ord, cfg->slice_begin, cfg->slice_end), cfg->samples_per_pixel, a, b);
+    if (b > a) w.n_orders = ord + 1;
+  }
 
   uint32_t launches = 0;
   CU(cudaMemsetAsync(f->counters, 0, sizeof(unsigned long long), f->stream));
@@ -337,6 +354,9 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
                        (size_t)(cfg->slice_end - cfg->slice_begin) * f->npix * sizeof(float4),
                        f->stream));
   } else {
+    for (uint32_t ord = w.n_orders; ord < n_own; ++ord)  // planes of the slices that are not queued
+      CU(cudaMemsetAsync(f->accum + (size_t)slice_in_order(ord, cfg->slice_begin, cfg->slice_end) * f->npix,
+                         0, (size_t)f->npix * sizeof(float4), f->stream));
     // path slots live in a pool in device memory (allocated on first use)
     if (!f->pool) {
       uint32_t slots = wave_default_slots(f->sm_count);
@@ -363,9 +383,11 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
   if (stats) {
     memset(stats, 0, sizeof *stats);
     uint64_t s0 = 0;
-    for (uint32_t k = cfg->slice_begin; k < cfg->slice_end; ++k)
-      s0 += ((uint64_t)(k + 1) * cfg->samples_per_pixel) / RT_SLICES -
-            ((uint64_t)k * cfg->samples_per_pixel) / RT_SLICES;
+    for (uint32_t k = cfg->slice_begin; k < cfg->slice_end; ++k) {
+      uint32_t a, b;
+      slice_range(k, cfg->samples_per_pixel, a, b);
+      s0 += b - a;
+    }
     stats->samples = s0 * f->npix;
     CU(cudaEventElapsedTime(&stats->render_ms, f->ev[0], f->ev[1]));
     stats->launches = launches;
@@ -379,6 +401,28 @@ extern "C" int rt_frame_reduce_local(rt_frame *f, const rt_config *cfg) {
   CU(cudaSetDevice(f->device));
   CU(launch_reduce_local(f->accum, f->npix, cfg->slice_begin, cfg->slice_end, f->partial,
                          f->sm_count, f->stream));
+  // the ray counts of this frame order the work queue of the next one (heaviest pixels first)
+  if (!f->order) {
+    f->sort_temp_bytes = cost_order_temp_bytes(f->npix);
+    CU(cudaMalloc(&f->order, (size_t)f->npix * 4));
+    CU(cudaMalloc(&f->sort_keys, (size_t)f->npix * 4));
+    CU(cudaMalloc(&f->sort_keys_out, (size_t)f->npix * 4));
+    CU(cudaMalloc(&f->sort_iota, (size_t)f->npix * 4));
+    CU(cudaMalloc(&f->sort_temp, f->sort_temp_bytes ? f->sort_temp_bytes : 16));
+    CU(cudaMalloc(&f->heavy, 4));
+  }
+  uint32_t own = 0;
+  for (uint32_t k = cfg->slice_begin; k < cfg->slice_end; ++k) {
+    uint32_t a, b;
+    slice_range(k, cfg->samples_per_pixel, a, b);
+    own += b - a;
+  }
+  if (own) {
+    CU(launch_cost_order(f->partial, f->npix, 1.0f / (float)own, f->sort_keys, f->sort_keys_out,
+                         f->sort_iota, f->order, f->heavy, f->sort_temp, f->sort_temp_bytes, f->sm_count,
+                         f->stream));
+    f->order_valid = true;
+  }
   CU(cudaStreamSynchronize(f->stream));
   return RT_OK;
 }

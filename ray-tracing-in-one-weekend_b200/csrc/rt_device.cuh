@@ -46,6 +46,36 @@ struct CameraF64 {
 // Relative slack of the f32 line-sphere filter (see DESIGN.md "filter error bound").
 #define RTB_FILTER_SLACK 1.9073486328125e-06f /* 32 * 2^-24 */
 
+// ---------------------------------------------------------------- canonical sample slices
+// The spp samples of a pixel are cut into 64 canonical slices in 8 blocks of 8.  Block b covers
+// [floor(b*spp/8), floor((b+1)*spp/8)); inside a block slices 0..3 each take half (rounded up) of
+// what the slices before them left, and slices 4..7 share the remaining sixteenth evenly
+// (31, 16, 8, 4, 1, 1, 1, 0 for 62 samples; 256, 128, 64, 32, 8, 8, 8, 8 for 512).  Work items
+// are handed out largest slices first, so a frame ends on its smallest items and the
+// end-of-frame tail stays short however few slices a GPU owns.
+__host__ __device__ __forceinline__ void slice_range(uint32_t k, uint32_t spp, uint32_t &begin,
+                                                     uint32_t &end) {
+  const uint32_t blk = k >> 3, j = k & 7u;
+  uint32_t lo = (uint32_t)(((uint64_t)blk * spp) >> 3);
+  const uint32_t hi = (uint32_t)(((uint64_t)(blk + 1) * spp) >> 3);
+  for (uint32_t i = 0; i < (j < 4u ? j : 4u); ++i) lo += (hi - lo + 1u) >> 1;
+  if (j < 4u) {
+    begin = lo;
+    end = lo + ((hi - lo + 1u) >> 1);
+  } else {
+    const uint32_t rest = hi - lo, q = j - 4u;  // quarter q of the rest, earlier quarters larger
+    begin = lo + (uint32_t)(((uint64_t)q * rest + 3u) >> 2);
+    end = lo + (uint32_t)(((uint64_t)(q + 1u) * rest + 3u) >> 2);
+  }
+}
+// order_idx-th slice of the aligned block [sb, se) in hand-out order (big slices first)
+__host__ __device__ __forceinline__ uint32_t slice_in_order(uint32_t order_idx, uint32_t sb, uint32_t se) {
+  const uint32_t cnt = se - sb;
+  if ((sb & 7u) || (cnt & 7u)) return sb + order_idx;
+  const uint32_t nb = cnt >> 3;
+  return sb + (order_idx % nb) * 8u + order_idx / nb;
+}
+
 // ---------------------------------------------------------------- Philox4x32-10
 // Stream contract (identical in oracle/rt_oracle.c):
 //   key = (pixel index in output order, absolute sample index)

@@ -16,6 +16,8 @@
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
+#include <cub/device/device_radix_sort.cuh>
+
 namespace rtb {
 
 // ---------------------------------------------------------------- slice tree + finalise
@@ -187,6 +189,58 @@ __global__ void __launch_bounds__(256) ffma_peak_kernel(float *out, int iters, f
 cudaError_t launch_ffma_peak(float *out, int blocks, int iters, long long *cycles,
                              cudaStream_t st) {
   ffma_peak_kernel<<<blocks, 256, 0, st>>>(out, iters, 0.999f, 0.001f, cycles);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- hand-out order by cost
+// Work items of a slice are handed out heaviest pixels first (cost = ray segments per sample of
+// the pixel in the frame rendered before on this frame object), so the items still in flight when
+// the work queue runs dry are the cheap ones and the end-of-frame tail is short.  The order only
+// schedules work: every item's sum is independent of it, and so is the image.
+__global__ void __launch_bounds__(256) cost_keys_kernel(const float4 *__restrict__ partial, uint32_t npix,
+                                                        float inv_samples, uint32_t *__restrict__ keys,
+                                                        uint32_t *__restrict__ iota) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+    // quarter-ray resolution, 8-bit key, ascending key = descending cost; the sort is stable, so
+    // pixels of equal cost keep their scan order (coherent neighbours stay neighbours)
+    const float q = __ldg(&partial[i]).w * inv_samples * 4.0f;
+    const uint32_t c = q >= 255.0f ? 255u : (uint32_t)q;
+    keys[i] = 255u - c;
+    iota[i] = i;
+  }
+}
+
+// number of leading entries of the sorted order whose cost is >= kHeavyRays rays per sample
+// (binary search in the sorted keys; ascending key = descending cost)
+__global__ void heavy_count_kernel(const uint32_t *__restrict__ sorted_keys, uint32_t npix,
+                                   uint32_t max_key, uint32_t *__restrict__ heavy) {
+  uint32_t lo = 0, hi = npix;  // first index with key > max_key
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (sorted_keys[mid] <= max_key) lo = mid + 1; else hi = mid;
+  }
+  *heavy = lo;
+}
+
+size_t cost_order_temp_bytes(uint32_t npix) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr,
+                                  (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)npix, 0, 8);
+  return bytes;
+}
+
+cudaError_t launch_cost_order(const float4 *partial, uint32_t npix, float inv_samples, uint32_t *keys,
+                              uint32_t *keys_out, uint32_t *iota, uint32_t *order, uint32_t *heavy,
+                              void *temp, size_t temp_bytes, int sm_count, cudaStream_t st) {
+  int grid = sm_count * 8;
+  cost_keys_kernel<<<grid, 256, 0, st>>>(partial, npix, inv_samples, keys, iota);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys, keys_out, iota, order, (int)npix, 0, 8, st);
+  if (e != cudaSuccess) return e;
+  // pixels whose paths are long on average (glass, facing mirrors) are where the rare 50-bounce
+  // paths live: ALL their slices are handed out before anything else
+  heavy_count_kernel<<<1, 1, 0, st>>>(keys_out, npix, 255u - 4u * kHeavyRays, heavy);
   return cudaGetLastError();
 }
 

@@ -37,9 +37,12 @@ struct WaveParams {
   uint64_t seed;
   uint32_t sample_offset;
   uint32_t slice_begin, slice_end;
+  uint32_t n_orders;            // slices handed out (hand-out order, trailing empty slices trimmed)
   float4 *accum;                // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
   unsigned long long *counter;  // work-queue head (zeroed before the frame)
   unsigned int *live;           // rays produced by the last polled shade pass
+  const uint32_t *order;        // pixel hand-out order within a slice (nullptr = scan order)
+  const uint32_t *heavy;        // leading pixels of `order` whose slices are all handed out first
   // pool of path slots (SoA, n_slots each)
   uint32_t n_slots;
   float4 *ray_o;       // {ox, oy, oz, |d| of the reference's un-normalised ray; < 0 = no ray}
@@ -75,6 +78,13 @@ void build_bvh(const double4 *spheres, uint32_t n, std::vector<BvhNode> &nodes,
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
                       bool use_bvh, int sm_count, size_t smem_optin_max, cudaStream_t st,
                       WaveRunInfo *info);
+
+// Pixel hand-out order by descending cost (ray segments per sample in `partial`), stable.
+size_t cost_order_temp_bytes(uint32_t npix);
+constexpr unsigned kHeavyRays = 5;  // rays per sample from which a pixel counts as "heavy"
+cudaError_t launch_cost_order(const float4 *partial, uint32_t npix, float inv_samples, uint32_t *keys,
+                              uint32_t *keys_out, uint32_t *iota, uint32_t *order, uint32_t *heavy,
+                              void *temp, size_t temp_bytes, int sm_count, cudaStream_t st);
 
 // dst[i] = canonical sub-tree sum of slices [slice_begin, slice_end) (aligned power of 2).
 cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t slice_begin,

@@ -247,15 +247,37 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
         P.accum[(size_t)(st.x >> kItemShift) * npix + (st.x & kItemPixelMask)] = A;
         st.x = 0xffffffffu;
       }
-      unsigned long long itq = atomicAdd(P.counter, 1ull);
+      // warp-aggregated pop: the lanes that need an item right now share ONE atomic (single-address
+      // atomics top out near 1 G/s, and a frame ends on one-sample items)
+      const unsigned am = __activemask();
+      const unsigned lane = threadIdx.x & 31u;
+      const int leader = __ffs((int)am) - 1;
+      unsigned long long itq = 0;
+      if ((int)lane == leader) itq = atomicAdd(P.counter, (unsigned long long)__popc(am));
+      itq = __shfl_sync(am, itq, leader) + (unsigned long long)__popc(am & ((1u << lane) - 1u));
       if (itq >= total_items) { depth = -1; break; }
-      uint32_t sl = (uint32_t)(itq / npix);
-      uint32_t px = (uint32_t)(itq - (uint64_t)sl * npix);
-      sl += P.slice_begin;
+      // hand-out order: first every slice of the heavy pixels, then the other pixels slice by
+      // slice (largest slices first, heaviest pixels first within a slice)
+      uint32_t ord, px;
+      if (P.order) {
+        const uint32_t nh = __ldg(P.heavy);
+        const uint64_t heavy_items = (uint64_t)nh * P.n_orders;
+        if (itq < heavy_items) {
+          ord = (uint32_t)(itq / nh);
+          px = __ldg(P.order + (uint32_t)(itq - (uint64_t)ord * nh));
+        } else {
+          const uint64_t q = itq - heavy_items;
+          const uint32_t nl = npix - nh;
+          ord = (uint32_t)(q / nl);
+          px = __ldg(P.order + nh + (uint32_t)(q - (uint64_t)ord * nl));
+        }
+      } else {
+        ord = (uint32_t)(itq / npix);
+        px = (uint32_t)(itq - (uint64_t)ord * npix);
+      }
+      const uint32_t sl = slice_in_order(ord, P.slice_begin, P.slice_end);
       st.x = sl << kItemShift | px;
-      // canonical slice k covers samples [floor(k*spp/S), floor((k+1)*spp/S)), S = RT_SLICES
-      st.y = (uint32_t)(((uint64_t)sl * P.spp) / RT_SLICES_DEV);
-      st.z = (uint32_t)(((uint64_t)(sl + 1) * P.spp) / RT_SLICES_DEV);
+      slice_range(sl, P.spp, st.y, st.z);
       A = make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
@@ -405,7 +427,7 @@ shade_kernel(const __grid_constant__ WaveParams P) {
   const float2 *aux = P.scene.aux;
   if (SMEM) stage_hit_rows(P, smem_raw, &s_bar, exact, mat, aux);
   const uint32_t npix = P.width * P.height;
-  const uint64_t total_items = (uint64_t)npix * (P.slice_end - P.slice_begin);
+  const uint64_t total_items = (uint64_t)npix * P.n_orders;
   uint32_t live_lanes = 0;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_slots; i += gridDim.x * blockDim.x)
     live_lanes += shade_slot<false>(P, i, exact, mat, aux, npix, total_items);
@@ -536,7 +558,7 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
   const float2 *aux = P.scene.aux;
   if (SMEM) stage_hit_rows(P, smem_raw, &s_bar, exact, mat, aux);
   const uint32_t npix = P.width * P.height;
-  const uint64_t total_items = (uint64_t)npix * (P.slice_end - P.slice_begin);
+  const uint64_t total_items = (uint64_t)npix * P.n_orders;
   const uint32_t stride = P.n_slots / R;
   const uint32_t base = blockIdx.x * kWBlock + threadIdx.x;  // grid * block == stride
 #pragma unroll 1
@@ -653,8 +675,11 @@ cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_c
 
   // every sample needs at least one wave of its slot: no need to poll before that many waves
   uint64_t total_samples = 0;
-  for (uint32_t k = p.slice_begin; k < p.slice_end; ++k)
-    total_samples += ((uint64_t)(k + 1) * p.spp) / RT_SLICES_DEV - ((uint64_t)k * p.spp) / RT_SLICES_DEV;
+  for (uint32_t k = p.slice_begin; k < p.slice_end; ++k) {
+    uint32_t a, b;
+    slice_range(k, p.spp, a, b);
+    total_samples += b - a;
+  }
   total_samples *= (uint64_t)p.width * p.height;
   const uint64_t min_waves = total_samples / p.n_slots;
   const uint32_t poll_every = 4;

@@ -4,8 +4,8 @@ The reference has no multi-device path; the rule here is the no
 each GPU renders a slice of the samples of EVERY pixel, partial sums travel to rank 0, and the
 image must not depend on the GPU count.  That is achieved without arithmetic in flight:
 
-  * the samples of a pixel are cut into SLICES = 64 canonical slices
-    [floor(k*spp/64), floor((k+1)*spp/64)); the path kernel sums each slice sequentially,
+  * the samples of a pixel are cut into SLICES = 64 canonical slices (`slice_samples`); the path
+    kernel sums each slice sequentially,
   * rank g of G (G in 1, 2, 4, 8) owns the aligned block of 64/G slices `slice_block(g, G)` and
     pre-sums exactly that sub-tree of the pairwise tree ((s0+s1)+(s2+s3))+... on its own GPU,
   * the [H*W] float4 partials are GATHERED to rank 0 in rank order (NCCL send/recv over
@@ -32,9 +32,19 @@ def slice_block(rank: int, world: int) -> tuple[int, int]:
 
 
 def slice_samples(k: int, spp: int) -> tuple[int, int]:
-    """Frame-relative sample range [begin, end) of canonical slice k (same formula as the
-    kernel, csrc/rt_path.cu)."""
-    return (k * spp) // SLICES, ((k + 1) * spp) // SLICES
+    """Frame-relative sample range [begin, end) of canonical slice k — the same rule as
+    slice_range() in csrc/rt_device.cuh: 8 blocks of 8 slices; block b covers
+    [floor(b*spp/8), floor((b+1)*spp/8)); inside a block slices 0..3 each take half (rounded up)
+    of what is left, slices 4..7 share the remaining sixteenth evenly
+    (31, 16, 8, 4, 1, 1, 1, 0 for 62 samples)."""
+    blk, j = divmod(k, 8)
+    lo, hi = (blk * spp) // 8, ((blk + 1) * spp) // 8
+    for _ in range(min(j, 4)):
+        lo += (hi - lo + 1) // 2
+    if j < 4:
+        return lo, lo + (hi - lo + 1) // 2
+    rest, q = hi - lo, j - 4
+    return lo + (q * rest + 3) // 4, lo + ((q + 1) * rest + 3) // 4
 
 
 def samples_of_block(begin: int, end: int, spp: int) -> int:

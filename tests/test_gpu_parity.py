@@ -142,3 +142,31 @@ def test_bit_exact_across_gpu_counts(rt):
         assert np.array_equal(lin, base_lin), f"G={G}: linear sums differ"
     other, _, _ = rt.render_image(scene, cam, rt.Config(W, H, spp, 50, seed=12))
     assert not np.array_equal(other, base_rgb)  # the seed matters
+
+
+def test_cost_ordered_handout_does_not_change_the_image(rt):
+    """A frame object orders the work queue of its next render by the ray counts of the previous
+    one (heaviest pixels first, csrc/rt_kernels.cu).  That is scheduling only: the image of a
+    re-used frame object must be byte-identical to a fresh one — also when the previous render
+    was a different scene."""
+    W, H, spp = 160, 90, 48
+    cover = rt.Scene(golden("cover_small.npz")["spheres"])
+    three = rt.Scene(golden("three_small.npz")["spheres"])
+    cam_c, cam_t = cam_for(rt, "cover", W, H), cam_for(rt, "three", W, H)
+    cfg = rt.Config(W, H, spp, 50, seed=21)
+
+    def render(frame, scene, cam):
+        frame.render(scene, cam, cfg)
+        frame.reduce_local(cfg)
+        rgb, lin, st = frame.finalize(cfg, want_linear=True)
+        return rgb.copy(), lin.copy(), st.rays
+
+    fresh = render(rt.Frame(W, H), cover, cam_c)
+    fr = rt.Frame(W, H)
+    first = render(fr, cover, cam_c)     # scan order
+    second = render(fr, cover, cam_c)    # ordered by the first render's costs
+    render(fr, three, cam_t)             # another scene in between
+    third = render(fr, cover, cam_c)     # ordered by the three-sphere scene's costs
+    for other in (first, second, third):
+        assert other[2] == fresh[2]
+        assert np.array_equal(other[0], fresh[0]) and np.array_equal(other[1], fresh[1])
