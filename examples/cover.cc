@@ -3,7 +3,7 @@
 // depth 50), P3 image on stdout and a human log on stderr.  The pixel loops are one call into
 // the sm_100a kernels (rt::render); nothing is traced on the CPU.
 //
-//   ./rt_cover [--scene cover|three|stress [--half H]] [--bvh] [--width W] [--aspect 16:9] [--spp N] [--depth D]
+//   ./rt_cover [--scene cover|three|stress [--half H]] [--bvh] [--gpus N] [--width W] [--aspect 16:9] [--spp N] [--depth D]
 //              [--seed S] [--out file.ppm] [--dump-scene file.f64] > image.ppm
 #include <chrono>
 #include <cstdlib>
@@ -22,6 +22,7 @@ int main(int argc, char **argv) {
   unsigned long long seed = 0;
   int half = 158;
   bool use_bvh = false;
+  int gpus = 1;
   for (int k = 1; k < argc; ++k) {
     std::string a = argv[k];
     auto val = [&]() -> const char * {
@@ -41,6 +42,7 @@ int main(int argc, char **argv) {
     else if (a == "--out") out = val();
     else if (a == "--half") half = std::atoi(val());
     else if (a == "--bvh") use_bvh = true;
+    else if (a == "--gpus") gpus = std::atoi(val());
     else if (a == "--dump-scene") dump = val();
     else { std::cerr << "unknown option " << a << "\n"; return 2; }
   }
@@ -77,7 +79,12 @@ int main(int argc, char **argv) {
             << "Spheres: " << world.objects.size() << "\n";
   try {
     auto t0 = std::chrono::high_resolution_clock::now();
-    image img = render(world, cam, image_width, image_height, samples_per_pixel, max_depth, seed, 0, use_bvh);
+    std::vector<int32_t> devices;
+    for (int g = 0; g < gpus; ++g) devices.push_back(g);
+    image img = gpus > 1 ? render_multi(world, cam, image_width, image_height, samples_per_pixel,
+                                        max_depth, devices, seed, use_bvh)
+                         : render(world, cam, image_width, image_height, samples_per_pixel, max_depth,
+                                  seed, 0, use_bvh);
     auto t1 = std::chrono::high_resolution_clock::now();
     img.write_ppm(out.c_str());
     double ms = std::chrono::duration<double, std::milli>(t1 - t0).count();

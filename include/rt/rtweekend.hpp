@@ -301,5 +301,24 @@ inline image render(const hittable_list &world, const camera &cam, uint32_t imag
   return img;
 }
 
+// The same frame with its samples split over several GPUs of this process; the image is
+// byte-identical to the single-GPU one.
+inline image render_multi(const hittable_list &world, const camera &cam, uint32_t image_width,
+                          uint32_t image_height, uint32_t samples_per_pixel, uint32_t max_depth,
+                          const std::vector<int32_t> &devices, uint64_t seed = 0, bool use_bvh = false) {
+  std::vector<rt_sphere> flat = world.flatten();
+  rt_config cfg{};
+  cfg.width = image_width; cfg.height = image_height;
+  cfg.samples_per_pixel = samples_per_pixel; cfg.max_depth = max_depth;
+  cfg.seed = seed; cfg.slice_begin = 0; cfg.slice_end = RT_SLICES;
+  cfg.flags = use_bvh ? RT_FLAG_BVH : 0u;
+  image img;
+  img.width = image_width; img.height = image_height;
+  img.rgb.resize((size_t)image_width * image_height * 3);
+  check(rt_render_image_multi(flat.data(), (uint32_t)flat.size(), &cam.abi(), &cfg, devices.data(),
+                              (uint32_t)devices.size(), img.rgb.data(), nullptr, &img.stats));
+  return img;
+}
+
 }  // namespace rt
 #endif

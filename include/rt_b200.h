@@ -124,6 +124,16 @@ int rt_finalize(rt_frame *, const rt_config *, const void *const *partials, uint
 int rt_render_image(const rt_scene *, const rt_camera *, const rt_config *, uint8_t *rgb8_out,
                     float *linear_out, rt_stats *);
 
+/* Same, with the frame's samples split over `ngpu` devices of this process (ngpu in {1,2,4,8}):
+ * one host thread per GPU renders its block of canonical slices, the per-GPU partial sums are
+ * copied to devices[0] over NVLink peer copies (no arithmetic in flight) and finalised there.
+ * The image is byte-identical for every ngpu.  (Multi-process deployments use rt_render +
+ * rt_frame_partial_ptr + rt_finalize with their own transport instead, see INTEGRATION.md.)
+ * The reference has no multi-device path. */
+int rt_render_image_multi(const rt_sphere *spheres, uint32_t n, const rt_camera *, const rt_config *,
+                          const int32_t *devices, uint32_t ngpu, uint8_t *rgb8_out,
+                          float *linear_out, rt_stats *);
+
 /* --- accuracy gate: pixel-centre, zero-lens primary rays, closest hit in reference order
  *     (hittable_list::hit + sphere::hit, src/cpu/hittable_list.h:28-43, sphere.h:24-51).
  *     use_f64 = 1: IEEE double without FMA contraction, op-for-op like the reference

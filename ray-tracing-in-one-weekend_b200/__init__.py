@@ -56,7 +56,7 @@ SYMBOLS = [
     "rt_last_error", "rt_version", "rt_device_count", "rt_scene_create", "rt_scene_destroy",
     "rt_scene_count", "rt_frame_create", "rt_frame_destroy", "rt_frame_partial_ptr", "rt_render",
     "rt_frame_reduce_local", "rt_finalize", "rt_render_image", "rt_primary_hits", "rt_write_ppm",
-    "rt_frame_set_stream", "rt_measure_fp32_peak",
+    "rt_frame_set_stream", "rt_measure_fp32_peak", "rt_render_image_multi",
 ]
 
 _lib = None
@@ -233,6 +233,20 @@ def render_image(scene: Scene, cam: Camera, cfg: Config, want_linear=True):
     _check(lib().rt_render_image(scene._h, C.byref(cc), C.byref(cf), C.c_void_p(rgb.ctypes.data),
                                  C.c_void_p(lin.ctypes.data) if lin is not None else None,
                                  C.byref(st)))
+    return rgb, lin, Stats.of(st)
+
+
+def render_image_multi(rows: np.ndarray, cam: Camera, cfg: Config, devices, want_linear=True):
+    """One process, several GPUs (rt_render_image_multi) -> (rgb8, linear sums, Stats)."""
+    arr, n = spheres_from_rows(rows)
+    rgb = np.empty((cfg.height, cfg.width, 3), np.uint8)
+    lin = np.empty((cfg.height, cfg.width, 3), np.float32) if want_linear else None
+    st, cc, cf = _Stats(), cam.c(), cfg.c()
+    devs = (C.c_int32 * len(devices))(*devices)
+    _check(lib().rt_render_image_multi(arr, C.c_uint32(n), C.byref(cc), C.byref(cf), devs,
+                                       C.c_uint32(len(devices)), C.c_void_p(rgb.ctypes.data),
+                                       C.c_void_p(lin.ctypes.data) if lin is not None else None,
+                                       C.byref(st)))
     return rgb, lin, Stats.of(st)
 
 

@@ -7,6 +7,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/rt_b200.h"
@@ -486,6 +488,87 @@ extern "C" int rt_render_image(const rt_scene *sc, const rt_camera *cam, const r
   }
   rt_frame_destroy(f);
   if (!rc && stats) *stats = st;
+  return rc;
+}
+
+// ---------------------------------------------------------------- one process, several GPUs
+extern "C" int rt_render_image_multi(const rt_sphere *spheres, uint32_t n, const rt_camera *cam,
+                                     const rt_config *cfg_in, const int32_t *devices, uint32_t ngpu,
+                                     uint8_t *rgb8_out, float *linear_out, rt_stats *stats) {
+  if (!cam || !cfg_in || !devices) return fail(RT_E_INVALID, "NULL argument");
+  if (!(ngpu == 1 || ngpu == 2 || ngpu == 4 || ngpu == 8))
+    return fail(RT_E_INVALID, "ngpu must be 1, 2, 4 or 8 (got %u)", ngpu);
+  for (uint32_t a = 0; a < ngpu; ++a)
+    for (uint32_t b = a + 1; b < ngpu; ++b)
+      if (devices[a] == devices[b]) return fail(RT_E_INVALID, "device %d listed twice", devices[a]);
+  std::vector<rt_scene *> scenes(ngpu, nullptr);
+  std::vector<rt_frame *> frames(ngpu, nullptr);
+  std::vector<rt_stats> st(ngpu);
+  std::vector<int> rcs(ngpu, RT_OK);
+  std::vector<std::string> errs(ngpu);
+  const uint32_t per = RT_SLICES / ngpu;
+  auto work = [&](uint32_t g) {
+    rt_config c = *cfg_in;
+    c.device = devices[g];
+    c.slice_begin = g * per; c.slice_end = (g + 1) * per;
+    int rc = rt_scene_create(spheres, n, c.device, &scenes[g]);
+    if (!rc) rc = rt_frame_create(c.width, c.height, c.device, &frames[g]);
+    memset(&st[g], 0, sizeof(rt_stats));
+    if (!rc) rc = rt_render(scenes[g], cam, &c, frames[g], &st[g]);
+    if (!rc) rc = rt_frame_reduce_local(frames[g], &c);
+    rcs[g] = rc;
+    if (rc) errs[g] = rt_last_error();  // the message is thread-local
+  };
+  {
+    std::vector<std::thread> th;
+    for (uint32_t g = 1; g < ngpu; ++g) th.emplace_back(work, g);
+    work(0);
+    for (auto &t : th) t.join();
+  }
+  int rc = RT_OK;
+  for (uint32_t g = 0; g < ngpu && !rc; ++g)
+    if (rcs[g]) rc = fail(rcs[g], "GPU %d: %s", devices[g], errs[g].c_str());
+  std::vector<float4 *> staged(ngpu, nullptr);
+  if (!rc) {
+    // partial sums of the other GPUs -> devices[0], bytes only (peer copy over NVLink when the
+    // topology allows it, through the host otherwise)
+    rt_frame *f0 = frames[0];
+    cudaError_t e = cudaSetDevice(devices[0]);
+    const size_t bytes = (size_t)f0->npix * sizeof(float4);
+    std::vector<const void *> parts(ngpu);
+    parts[0] = f0->partial;
+    for (uint32_t g = 1; g < ngpu && e == cudaSuccess; ++g) {
+      int can = 0;
+      if (cudaDeviceCanAccessPeer(&can, devices[0], devices[g]) == cudaSuccess && can) {
+        cudaError_t pe = cudaDeviceEnablePeerAccess(devices[g], 0);
+        if (pe != cudaSuccess) (void)cudaGetLastError();  // already enabled
+      }
+      e = cudaMalloc(&staged[g], bytes);
+      if (e == cudaSuccess) e = cudaMemcpyPeer(staged[g], devices[0], frames[g]->partial, devices[g], bytes);
+      parts[g] = staged[g];
+    }
+    if (e != cudaSuccess) rc = fail(RT_E_CUDA, "gathering partial sums failed: %s", cudaGetErrorString(e));
+    rt_config call = *cfg_in;
+    call.device = devices[0]; call.slice_begin = 0; call.slice_end = RT_SLICES;
+    rt_stats fin;
+    memset(&fin, 0, sizeof fin);
+    if (!rc) rc = rt_finalize(f0, &call, parts.data(), ngpu, rgb8_out, linear_out, &fin);
+    if (!rc && stats) {
+      *stats = fin;
+      stats->samples = 0; stats->render_ms = 0.f;
+      for (uint32_t g = 0; g < ngpu; ++g) {
+        stats->samples += st[g].samples;
+        stats->launches += st[g].launches + 1;
+        if (st[g].render_ms > stats->render_ms) stats->render_ms = st[g].render_ms;
+      }
+      stats->frame_ms = stats->render_ms + fin.finalize_ms;
+    }
+  }
+  for (uint32_t g = 0; g < ngpu; ++g) {
+    if (staged[g]) { cudaSetDevice(devices[0]); cudaFree(staged[g]); }
+    rt_frame_destroy(frames[g]);
+    rt_scene_destroy(scenes[g]);
+  }
   return rc;
 }
 
