@@ -215,14 +215,15 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
                                (int)P.cand_idx[(size_t)1 * P.n_slots + i]);
     } else {
       const uint32_t cnt = P.cand_cnt[i];
+      const uint32_t skip = (uint32_t)__float_as_int(RD.w);  // the sphere the ray just left, or -1
       if (cnt <= kCandPlanes) {
         for (uint32_t k = 0; k < cnt; ++k) {
           const uint32_t s = P.cand_idx[(size_t)k * P.n_slots + i];
-          if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+          if (s != skip && wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
         }
       } else {  // candidate planes overflowed: exact test of every sphere (rare)
         for (uint32_t s = 0; s < P.scene.n; ++s)
-          if (wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+          if (s != skip && wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
       }
     }
     if (id < 0) {
@@ -309,7 +310,8 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       float ddy = P.cam.llc_minus_origin[1] + u * P.cam.horizontal[1] + v * P.cam.vertical[1] - offy;
       float ddz = P.cam.llc_minus_origin[2] + u * P.cam.horizontal[2] + v * P.cam.vertical[2] - offz;
       float len = sqrtf(ddx * ddx + ddy * ddy + ddz * ddz), inv = 1.0f / len;
-      RD.x = ddx * inv; RD.y = ddy * inv; RD.z = ddz * inv; RD.w = 0.f;
+      RD.x = ddx * inv; RD.y = ddy * inv; RD.z = ddz * inv;
+      RD.w = __int_as_float(-1);  // no sphere to skip
       RO.w = len;
       T.x = T.y = T.z = 1.0f;
       depth = (int)P.max_depth;
@@ -372,6 +374,13 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
         float len = sqrtf(sx * sx + sy * sy + sz * sz), inv = 1.0f / len;
         RD.x = sx * inv; RD.y = sy * inv; RD.z = sz * inv;
         RO.w = len;
+        // A ray that starts on a sphere and points away from its centre side never meets that
+        // sphere again: (p - c).d > 0 (clearly, not within rounding of the tangent plane).  Its
+        // line still passes the filter, so the resolve pass is told to skip that candidate; this
+        // also removes the f32-origin self-hits the t_min = 0.001 rule (main.cc:19) cannot catch
+        // at grazing angles on the r = 1000 ground sphere.
+        const float away = (RD.x * onx + RD.y * ony + RD.z * onz) * ((float)S.w > 0.f ? 1.f : -1.f);
+        RD.w = __int_as_float(away > 1e-3f ? id : -1);
       } else {
         RO.w = -1.0f;  // no ray this wave: the path regenerates in the next one
       }
@@ -463,6 +472,7 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
     ray.tminA = 0.001 * (double)o.w * ray.a;
     double bestN = __longlong_as_double(0x7ff0000000000000ll);
     int id = -1;
+    const uint32_t skip = (uint32_t)__float_as_int(d.w);
     const float tmin_f = 0.001f * o.w * 0.9999f;
     float tbest = __int_as_float(0x7f800000);  // upper bound of the best root (unit-direction t)
     const float ix = 1.0f / (fabsf(d.x) > 1e-30f ? d.x : copysignf(1e-30f, d.x));
@@ -497,6 +507,7 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
       if (count) {
         for (uint32_t k = 0; k < count; ++k) {
           const uint32_t s = __ldg(prim + first + k);
+          if (s == skip) continue;  // the sphere the ray just left (see shade_slot)
           const float4 S = __ldg(fast + s);
           const float b = fmaf(S.x, d.x, fmaf(S.y, d.y, fmaf(S.z, d.z, nod)));
           const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
