@@ -644,7 +644,7 @@ static cudaError_t launch_filter_t(const WaveParams &p, const ConstRows &cr, boo
 cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_count,
                           size_t smem_optin_max, cudaStream_t st, unsigned int *host_live,
                           WaveRunInfo *info) {
-  static ConstRows cr;
+  static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
   const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
                      !getenv("RT_B200_NO_CONST_ROWS");
   if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
@@ -752,7 +752,7 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
                       bool use_bvh, int sm_count, size_t smem_optin_max, cudaStream_t st,
                       WaveRunInfo *info) {
   if (use_bvh && !p.scene.bvh_nodes) return cudaErrorInvalidValue;
-  static ConstRows cr;
+  static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
   const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
                      !getenv("RT_B200_NO_CONST_ROWS");
   if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));

@@ -62,8 +62,8 @@ def test_primary_f32_production_path(rt, name):
 @pytest.mark.parametrize("name,W,H,spp", [("three", 96, 54, 32), ("cover", 64, 36, 16)])
 def test_same_stream_vs_oracle(rt, orc, name, W, H, spp):
     """CUDA f32 path vs oracle f64 path driven by the SAME Philox stream: paths only diverge
-    where rounding flips a discrete decision.  Tolerance: median |diff| < 1e-5, mean < 2e-3
-    (linear radiance per pixel), ray counts within 0.5 %."""
+    where rounding flips a discrete decision.  Tolerance: median |diff| < 1e-6, mean < 5e-5
+    (linear radiance per pixel), ray counts within 0.2 %."""
     rows = golden(f"{name}_small.npz")["spheres"]
     scene = rt.Scene(rows)
     rgb, lin, st = rt.render_image(scene, cam_for(rt, name, W, H), rt.Config(W, H, spp, 50, seed=7))
@@ -71,17 +71,18 @@ def test_same_stream_vs_oracle(rt, orc, name, W, H, spp):
                                      mode=orc.RNG_PHILOX, seed=7)
     err = np.abs(lin / spp - olin / spp)
     assert st.samples == samples == W * H * spp
-    assert np.median(err) < 1e-5
-    assert err.mean() < 2e-3
-    assert abs(st.rays - rays) / rays < 5e-3
+    # measured (tools/parity_report.py): median 7e-9..9e-9, mean 2e-7..2e-6, ray counts within 4e-4
+    assert np.median(err) < 1e-6
+    assert err.mean() < 5e-5
+    assert abs(st.rays - rays) / rays < 2e-3
     assert st.sphere_tests == st.rays * len(rows)
     # 8-bit image: identical except at quantisation boundaries / diverged paths
     oq = orc.write_color(olin, spp)
-    assert (np.abs(rgb.astype(int) - oq.astype(int)) > 1).mean() < 0.02
+    assert (np.abs(rgb.astype(int) - oq.astype(int)) > 1).mean() < 2e-3
 
 
 def test_single_sample_parity(rt, orc):
-    """spp = 1 with sample_offset: every pixel is ONE path; >= 99 % of paths must agree with the
+    """spp = 1 with sample_offset: every pixel is ONE path; >= 99.9 % of paths must agree with the
     f64 oracle to 1e-4 (the rest are legitimately diverged by rounding)."""
     name, W, H = "three", 128, 72
     rows = golden(f"{name}_small.npz")["spheres"]
@@ -92,7 +93,7 @@ def test_single_sample_parity(rt, orc):
         olin, _, _ = orc.render(rows, orc.scene_camera(name, W, H), W, H, 1, mode=orc.RNG_PHILOX,
                                 seed=3, sample_offset=off)
         close = np.abs(lin - olin).max(axis=2) < 1e-4
-        assert close.mean() >= 0.99, close.mean()
+        assert close.mean() >= 0.999, close.mean()
 
 
 # ----------------------------------------------------------------- gate 2: converged renders
