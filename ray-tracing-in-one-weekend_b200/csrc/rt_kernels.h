@@ -27,7 +27,8 @@ struct ConstRows {
 };
 
 // ---------------------------------------------------------------- wavefront form (rt_wave.cu)
-constexpr unsigned kCandPlanes = 16;  // candidate indices kept per ray before the exact full scan
+constexpr unsigned kCandPlanes = 16;  // candidate entries kept per ray before the exact full scan
+constexpr unsigned kCandShift = 8;    // entry = first row of a decision group << kCandShift | row mask
 
 struct WaveParams {
   SceneView scene;
@@ -50,8 +51,8 @@ struct WaveParams {
   float4 *thr;         // {throughput r, g, b, depth (int bits): >0 bounces left, 0 new path, -1 retired}
   float4 *acc;         // {item sum r, g, b, ray segments}
   uint4 *it;           // {slice << kItemShift | pixel, next sample, slice end, -}
-  uint32_t *cand_cnt;  // filter survivors per ray (> kCandPlanes = overflow)
-  uint32_t *cand_idx;  // [kCandPlanes][n_slots] sphere indices, ascending
+  uint32_t *cand_cnt;  // candidate entries per ray (> kCandPlanes = overflow)
+  uint32_t *cand_idx;  // [kCandPlanes][n_slots] {group << kCandShift | row mask}, ascending
 };
 
 struct WaveRunInfo {

@@ -93,17 +93,17 @@ __device__ __forceinline__ void filter_rays(const WaveParams &P, const ConstRows
         any = any | (mx[p] >= OOT[p].x) | (my[p] >= OOT[p].y);  // no short-circuit: independent compares
       }
       if (__any_sync(0xffffffffu, any)) {
-        // rare path, narrowed ray by ray: only a ray whose group maximum passed looks at its rows
+        // rare path, narrowed ray by ray: a ray whose group maximum passed records the group and
+        // the mask of its rows that passed as ONE candidate entry {s0 << kCandShift | mask}
 #pragma unroll
         for (int r = 0; r < R; ++r)
           if (((r & 1) ? my[r >> 1] : mx[r >> 1]) >= WPK(OOT, r)) {
+            uint32_t m = 0;
 #pragma unroll
-            for (int k = 0; k < G; ++k)
-              if (WPK(e[k], r) >= WPK(OOT, r)) {
-                if (cnt[r] < kCandPlanes) cand[off[r]] = s0 + k;
-                off[r] += nslots;
-                cnt[r] += 1;
-              }
+            for (int k = 0; k < G; ++k) m |= WPK(e[k], r) >= WPK(OOT, r) ? (1u << k) : 0u;
+            if (cnt[r] < kCandPlanes) cand[off[r]] = s0 << kCandShift | m;
+            off[r] += nslots;
+            cnt[r] += 1;
           }
       }
     };
@@ -217,8 +217,19 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       const uint32_t cnt = P.cand_cnt[i];
       const uint32_t skip = (uint32_t)__float_as_int(RD.w);  // the sphere the ray just left, or -1
       if (cnt <= kCandPlanes) {
-        for (uint32_t k = 0; k < cnt; ++k) {
-          const uint32_t s = P.cand_idx[(size_t)k * P.n_slots + i];
+        // entries {first row of a group << kCandShift | mask of its rows that passed}, ascending;
+        // one exact test per trip so that lanes with different entry shapes stay together
+        uint32_t k = 0, m = 0, s0 = 0;
+        for (;;) {
+          if (m == 0u) {
+            if (k == cnt) break;
+            const uint32_t e = P.cand_idx[(size_t)k * P.n_slots + i];
+            ++k;
+            s0 = e >> kCandShift;
+            m = e & ((1u << kCandShift) - 1u);
+          }
+          const uint32_t s = s0 + (uint32_t)__ffs((int)m) - 1u;
+          m &= m - 1u;
           if (s != skip && wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
         }
       } else {  // candidate planes overflowed: exact test of every sphere (rare)
