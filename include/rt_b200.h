@@ -68,6 +68,18 @@ typedef struct rt_config {
 #define RT_FLAG_WAVEFRONT 4u  /* two-kernel shade/filter wavefront instead of the fused persistent kernel */
 #define RT_FLAG_BVH 8u        /* closest hit through the host-built BVH instead of the brute-force scan
                                  over the reference's sphere order (same hit, same image) */
+#define RT_FLAG_V4_MODEL 16u  /* the semantics of the reference's CUDA program (src/gpu/, v4 book) instead
+                                 of src/cpu/: pixel-square sampling over W x H pixel footprints
+                                 (src/gpu/camera.h:140-167), metal fuzz point ON the unit sphere
+                                 (src/gpu/material.h:52), strict root interval so that the EARLIER of two
+                                 spheres with equal roots wins (src/gpu/sphere.h:31-36, interval.h:19-21).
+                                 rt_camera.aperture = 2 * focus_dist * tan(defocus_angle / 2). */
+#define RT_FLAG_F32_HIT 32u   /* compatibility/diagnostic: resolve the filter's candidates with the f32
+                                 sphere::hit arithmetic of src/gpu/sphere.h:15-47 (un-normalised direction,
+                                 f32 hit point, no self-skip) instead of f64.  Reproduces the cancellation of
+                                 |oc|^2 - r^2 on the r = 1000 ground sphere that darkens the reference CUDA
+                                 program's ground; brute-force fused mode only (not with RT_FLAG_BVH /
+                                 RT_FLAG_WAVEFRONT). */
 
 typedef struct rt_stats {
   uint64_t samples;      /* samples traced by this call */

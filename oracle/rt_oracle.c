@@ -242,6 +242,16 @@ int orc_three_scene(double *sp, int cap) { /* archive/listing69/main.cc:43-71 */
 #undef ORC_ADD
 }
 
+/* ------------------------------------------------------------------ model switch
+ * ORC_MODEL_CPU  = src/cpu/ (the spec, default).
+ * ORC_MODEL_GPU  = the semantics of the reference's CUDA program src/gpu/ (v4 book), restated in
+ *                  f64: strict root interval (src/gpu/sphere.h:31-36 + interval.h:19-21), metal
+ *                  fuzz point on the unit sphere (src/gpu/material.h:52), W x H pixel footprints
+ *                  (src/gpu/camera.h:92-103,140-157).  Philox mode only. */
+static int g_model = ORC_MODEL_CPU;
+void orc_set_model(int model) { g_model = model; }
+int orc_get_model(void) { return g_model; }
+
 /* ------------------------------------------------------------------ intersection */
 typedef struct { v3 p, normal; double t; int front_face; int id; } hitrec;
 
@@ -257,7 +267,12 @@ static int sphere_hit(const double *s, v3 org, v3 dir, double t_min, double t_ma
   if (discriminant < 0) return 0;
   double sqrtd = sqrt(discriminant);
   double root = (-half_b - sqrtd) / a;
-  if (root < t_min || t_max < root) {
+  if (g_model == ORC_MODEL_GPU) { /* !ray_t.surrounds(root), src/gpu/sphere.h:31-36 */
+    if (!(t_min < root && root < t_max)) {
+      root = (-half_b + sqrtd) / a;
+      if (!(t_min < root && root < t_max)) return 0;
+    }
+  } else if (root < t_min || t_max < root) {
     root = (-half_b + sqrtd) / a;
     if (root < t_min || t_max < root) return 0;
   }
@@ -357,6 +372,7 @@ static int scatter(const double *s, v3 dir_in, const hitrec *rec, rng_t *g, v3 *
   if (kind == ORC_METAL) {
     v3 reflected = vreflect(vunit(dir_in), rec->normal);
     v3 ball = g->mode == ORC_RNG_MT19937 ? mt_in_unit_sphere(g->c)
+              : g_model == ORC_MODEL_GPU ? direct_unit_vector(xi[0], xi[1]) /* src/gpu/material.h:52 */
                                          : direct_in_unit_sphere(xi[0], xi[1], xi[2]);
     *dir_out = vadd(reflected, vscale(s[8], ball));
     *atten = V(s[5], s[6], s[7]);
@@ -441,6 +457,12 @@ void orc_render(orc_ctx *c, const double *spheres, int n, const orc_camera *cam,
         }
         double u = (i + xu) / (W - 1);
         double v = (j + xv) / (H - 1);
+        if (g_model == ORC_MODEL_GPU) {
+          /* pixel00 + i du + row dv + (xi-1/2)(du + dv), src/gpu/camera.h:140-157, written from
+           * the lower-left corner: the vertical jitter is 1 - xi there (same distribution) */
+          u = (i + xu) / W;
+          v = (j + xv) / H;
+        }
         if (rng_mode == ORC_RNG_MT19937) disk = mt_in_unit_disk(c);
         /* camera::get_ray, src/cpu/camera.h:28-35 */
         v3 rd = vscale(cam->lens_radius, disk);

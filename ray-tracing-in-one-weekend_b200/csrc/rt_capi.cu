@@ -221,7 +221,7 @@ static void derive_camera(const rt_camera *c, CamFrame *f) {
   f->lens_radius = c->aperture / 2;
 }
 
-static CameraF32 narrow_camera(const CamFrame &f, uint32_t W, uint32_t H) {
+static CameraF32 narrow_camera(const CamFrame &f, uint32_t W, uint32_t H, bool pixel_square = false) {
   CameraF32 c;
   for (int k = 0; k < 3; ++k) {
     c.origin[k] = (float)f.origin[k];
@@ -230,8 +230,11 @@ static CameraF32 narrow_camera(const CamFrame &f, uint32_t W, uint32_t H) {
     c.u[k] = (float)f.u[k]; c.v[k] = (float)f.v[k];
   }
   c.lens_radius = (float)f.lens_radius;
-  c.inv_wm1 = (float)(1.0 / (double)(W - 1));
-  c.inv_hm1 = (float)(1.0 / (double)(H - 1));
+  // src/cpu/main.cc:116-117 divides by W-1 / H-1; the v4 camera (src/gpu/camera.h:92-103,140-157)
+  // tiles the viewport with W x H pixel footprints: pixel00 + i du + j dv + (xi - 1/2)(du + dv)
+  // = upper_left + (i + xi) viewport_u / W + (j + xi) viewport_v / H
+  c.inv_wm1 = (float)(1.0 / (double)(pixel_square ? W : W - 1));
+  c.inv_hm1 = (float)(1.0 / (double)(pixel_square ? H : H - 1));
   return c;
 }
 
@@ -308,12 +311,15 @@ static int check_cfg(const rt_config *cfg, const rt_frame *f) {
     return fail(RT_E_INVALID, "slices [%u,%u) must be an aligned power-of-two block of %u",
                 cfg->slice_begin, cfg->slice_end, RT_SLICES);
   if (cfg->samples_per_pixel == 0) return fail(RT_E_INVALID, "samples_per_pixel must be > 0");
+  if ((cfg->flags & RT_FLAG_F32_HIT) && (cfg->flags & (RT_FLAG_BVH | RT_FLAG_WAVEFRONT)))
+    return fail(RT_E_INVALID, "RT_FLAG_F32_HIT works with the brute-force fused kernel only");
   return RT_OK;
 }
 
 // ---------------------------------------------------------------- the hot path
 // 0 = fused persistent kernel (default), 2 = two-kernel wavefront (A/B variant of the same code)
 static int render_mode(const rt_config *cfg) {
+  if (cfg->flags & RT_FLAG_F32_HIT) return 0;
   if (const char *e = getenv("RT_B200_MODE")) return strcmp(e, "wave") == 0 ? 2 : 0;
   return (cfg->flags & RT_FLAG_WAVEFRONT) ? 2 : 0;
 }
@@ -329,7 +335,8 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
   derive_camera(cam, &cf);
   WaveParams w;
   w.scene = view_of(sc);
-  w.cam = narrow_camera(cf, f->w, f->h);
+  w.model_v4 = (cfg->flags & RT_FLAG_V4_MODEL) ? 1u : 0u;
+  w.cam = narrow_camera(cf, f->w, f->h, w.model_v4 != 0u);
   w.width = f->w; w.height = f->h;
   w.spp = cfg->samples_per_pixel; w.max_depth = cfg->max_depth;
   w.seed = cfg->seed; w.sample_offset = cfg->sample_offset;
@@ -376,7 +383,7 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
       CU(run_wavefront(w, sc->host_fast.data(), f->sm_count, f->smem_optin, f->stream, f->host_live, &info));
     } else {
       CU(run_fused(w, f->pool, f->pool_slots, sc->host_fast.data(), (cfg->flags & RT_FLAG_BVH) != 0,
-                   f->sm_count, f->smem_optin, f->stream, &info));
+                   (cfg->flags & RT_FLAG_F32_HIT) != 0, f->sm_count, f->smem_optin, f->stream, &info));
     }
     launches = info.launches;
   }

@@ -39,6 +39,7 @@ struct WaveParams {
   uint32_t sample_offset;
   uint32_t slice_begin, slice_end;
   uint32_t n_orders;            // slices handed out (hand-out order, trailing empty slices trimmed)
+  uint32_t model_v4;            // 1 = src/gpu semantics (RT_FLAG_V4_MODEL): strict root interval, fuzz on the sphere
   float4 *accum;                // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
   unsigned long long *counter;  // work-queue head (zeroed before the frame)
   unsigned int *live;           // rays produced by the last polled shade pass
@@ -76,8 +77,9 @@ void build_bvh(const double4 *spheres, uint32_t n, std::vector<BvhNode> &nodes,
 
 // Fused persistent form: one launch per frame; carves n_slots = grid * block * R out of the pool.
 // use_bvh: closest hit by BVH traversal (scene.bvh_nodes) instead of the brute-force filter.
+// f32_hit: candidate resolution in f32 like src/gpu/sphere.h (RT_FLAG_F32_HIT; brute force only).
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
-                      bool use_bvh, int sm_count, size_t smem_optin_max, cudaStream_t st,
+                      bool use_bvh, bool f32_hit, int sm_count, size_t smem_optin_max, cudaStream_t st,
                       WaveRunInfo *info);
 
 // Pixel hand-out order by descending cost (ray segments per sample in `partial`), stable.

@@ -163,7 +163,9 @@ struct WRay {
 
 // sphere::hit on numerators (root = N / a, a common to the ray): src/cpu/sphere.h:24-51 with the
 // inclusive upper bound of hittable_list.h:34-39 (a later sphere with an equal root wins).
-__device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, double &bestN) {
+// strict = the v4 interval of src/gpu/sphere.h:31-36 (t_min < root < t_max: the earlier sphere wins).
+__device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, double &bestN,
+                                               const bool strict) {
   double ocx = r.ox - S.x, ocy = r.oy - S.y, ocz = r.oz - S.z;
   double half_b = ocx * r.dx + ocy * r.dy + ocz * r.dz;
   double c = ocx * ocx + ocy * ocy + ocz * ocz - S.w * S.w;
@@ -171,9 +173,9 @@ __device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, d
   if (disc < 0.0) return false;
   double sq = wave_dsqrt(disc);
   double N = -half_b - sq;
-  if (N < r.tminA || bestN < N) {
+  if (strict ? (N <= r.tminA || bestN <= N) : (N < r.tminA || bestN < N)) {
     N = -half_b + sq;
-    if (N < r.tminA || bestN < N) return false;
+    if (strict ? (N <= r.tminA || bestN <= N) : (N < r.tminA || bestN < N)) return false;
   }
   bestN = N;
   return true;
@@ -184,7 +186,7 @@ __device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, d
 // a new path (miss / empty slot) or the scatter sample of the hit.  (3) camera::get_ray or
 // material::scatter.  A path that ends at a hit (absorbed, bounce limit) leaves the slot without a
 // ray for one wave and regenerates in the next one.  Returns 0 once the slot is retired.
-template <bool BVH>
+template <bool BVH, bool F32HIT = false>
 __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32_t i,
                                                const double4 *exact, const float4 *mat,
                                                const float2 *aux, const uint32_t npix,
@@ -213,8 +215,54 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       id = (int)P.cand_idx[i];
       bestN = __hiloint2double((int)P.cand_idx[(size_t)2 * P.n_slots + i],
                                (int)P.cand_idx[(size_t)1 * P.n_slots + i]);
+    } else if (F32HIT) {
+      // RT_FLAG_F32_HIT: sphere::hit in f32 on the reference's un-normalised direction, op for op
+      // src/gpu/sphere.h:15-47 (no self-skip, f32 hit point) -- reproduces the cancellation of
+      // |oc|^2 - r^2 on the r = 1000 ground sphere that the reference's CUDA program shows
+      const uint32_t cnt = P.cand_cnt[i];
+      const bool strict = P.model_v4 != 0u;
+      const float ddx = RD.x * RO.w, ddy = RD.y * RO.w, ddz = RD.z * RO.w;
+      const float a = ddx * ddx + ddy * ddy + ddz * ddz;
+      float bestT = __int_as_float(0x7f800000);
+      auto hit32 = [&](const uint32_t s) {
+        const double4 S = exact[s];
+        const float r = (float)S.w;
+        const float ocx = RO.x - (float)S.x, ocy = RO.y - (float)S.y, ocz = RO.z - (float)S.z;
+        const float hb = ocx * ddx + ocy * ddy + ocz * ddz;
+        const float c = ocx * ocx + ocy * ocy + ocz * ocz - r * r;
+        const float disc = hb * hb - a * c;
+        if (disc < 0.0f) return;
+        const float sq = sqrtf(disc);
+        float root = (-hb - sq) / a;
+        if (strict ? !(0.001f < root && root < bestT) : (root < 0.001f || bestT < root)) {
+          root = (-hb + sq) / a;
+          if (strict ? !(0.001f < root && root < bestT) : (root < 0.001f || bestT < root)) return;
+        }
+        bestT = root;
+        id = (int)s;
+      };
+      if (cnt <= kCandPlanes) {
+        uint32_t k = 0, m = 0, s0 = 0;
+        for (;;) {
+          if (m == 0u) {
+            if (k == cnt) break;
+            const uint32_t e = P.cand_idx[(size_t)k * P.n_slots + i];
+            ++k;
+            s0 = e >> kCandShift;
+            m = e & ((1u << kCandShift) - 1u);
+          }
+          hit32(s0 + (uint32_t)__ffs((int)m) - 1u);
+          m &= m - 1u;
+        }
+      } else {
+        for (uint32_t s = 0; s < P.scene.n; ++s) hit32(s);
+      }
+      if (id >= 0) {  // ray::at in f32 (src/gpu/ray.h), kept as the slot's f64 hit point
+        hpx = (double)fmaf(bestT, ddx, RO.x); hpy = (double)fmaf(bestT, ddy, RO.y); hpz = (double)fmaf(bestT, ddz, RO.z);
+      }
     } else {
       const uint32_t cnt = P.cand_cnt[i];
+      const bool strict = P.model_v4 != 0u;
       const uint32_t skip = (uint32_t)__float_as_int(RD.w);  // the sphere the ray just left, or -1
       if (cnt <= kCandPlanes) {
         // entries {first row of a group << kCandShift | mask of its rows that passed}, ascending;
@@ -230,11 +278,11 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
           }
           const uint32_t s = s0 + (uint32_t)__ffs((int)m) - 1u;
           m &= m - 1u;
-          if (s != skip && wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+          if (s != skip && wave_exact_hit(exact[s], ray, bestN, strict)) id = (int)s;
         }
       } else {  // candidate planes overflowed: exact test of every sphere (rare)
         for (uint32_t s = 0; s < P.scene.n; ++s)
-          if (s != skip && wave_exact_hit(exact[s], ray, bestN)) id = (int)s;
+          if (s != skip && wave_exact_hit(exact[s], ray, bestN, strict)) id = (int)s;
       }
     }
     if (id < 0) {
@@ -245,7 +293,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       A.y += T.y * (w + t * 0.7f);
       A.z += T.z * (w + t * 1.0f);
       depth = 0;
-    } else {
+    } else if (!F32HIT) {
       const double t = bestN * (2.0 - ray.a);  // 1/a = 2 - a to within eps^2 (a = 1 + eps)
       hpx = ray.ox + t * ray.dx; hpy = ray.oy + t * ray.dy; hpz = ray.oz + t * ray.dz;
     }
@@ -352,7 +400,9 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
         } else {
           sx = dx - 2.0f * dn * nx; sy = dy - 2.0f * dn * ny; sz = dz - 2.0f * dn * nz;
           if (M.w > 0.0f) {
-            float k = M.w * cbrtf(xi.z);
+            // src/cpu/material.h:43 draws the fuzz point inside the unit ball, the v4 model
+            // (src/gpu/material.h:52) on the unit sphere
+            float k = P.model_v4 ? M.w : M.w * cbrtf(xi.z);
             sx += k * ux; sy += k * uy; sz += k * uz;
           }
           alive = (sx * nx + sy * ny + sz * nz) > 0.0f;
@@ -391,7 +441,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
         // also removes the f32-origin self-hits the t_min = 0.001 rule (main.cc:19) cannot catch
         // at grazing angles on the r = 1000 ground sphere.
         const float away = (RD.x * onx + RD.y * ony + RD.z * onz) * ((float)S.w > 0.f ? 1.f : -1.f);
-        RD.w = __int_as_float(away > 1e-3f ? id : -1);
+        RD.w = __int_as_float(away > 1e-3f && !F32HIT ? id : -1);
       } else {
         RO.w = -1.0f;  // no ray this wave: the path regenerates in the next one
       }
@@ -471,6 +521,7 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
   const BvhNode *nodes = P.scene.bvh_nodes;
   const uint32_t *prim = P.scene.bvh_prim;
   const float4 *fast = P.scene.fast;
+  const bool strict = P.model_v4 != 0u;
 #pragma unroll 1
   for (int r = 0; r < R; ++r) {
     const uint32_t slot = base + r * stride;
@@ -531,8 +582,15 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
             if (disc >= 0.0) {
               double sq = wave_dsqrt(disc);
               double N = -half_b - sq;
-              if (N < ray.tminA) N = -half_b + sq;
-              if (N >= ray.tminA && (N < bestN || (N == bestN && (int)s > id))) {
+              bool take;
+              if (strict) {  // v4: t_min < root, equal roots keep the SMALLER index
+                if (N <= ray.tminA) N = -half_b + sq;
+                take = N > ray.tminA && (N < bestN || (N == bestN && (int)s < id));
+              } else {
+                if (N < ray.tminA) N = -half_b + sq;
+                take = N >= ray.tminA && (N < bestN || (N == bestN && (int)s > id));
+              }
+              if (take) {
                 bestN = N; id = (int)s;
                 tbest = (float)(N * 1.00001) + 1e-6f;
               }
@@ -570,7 +628,7 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
 // loop, state in the pool) and filter (R rays at once, registers hold nothing but rays).  No
 // kernel boundary, no inter-lane dependency; warps of an SM drift apart, so the latency-bound
 // shade phases of some warps overlap the FMA-pipe-bound filter phases of the others.
-template <int R, int G, bool CROWS, bool SMEM, bool BVH>
+template <int R, int G, bool CROWS, bool SMEM, bool BVH, bool F32HIT = false>
 __global__ void __launch_bounds__(kWBlock, RTW_MINB)
 fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -593,7 +651,7 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
   for (;;) {
     uint32_t live = 0;
 #pragma unroll 1
-    for (int r = 0; r < R; ++r) live += shade_slot<BVH>(P, base + r * stride, exact, mat, aux, npix, total_items);
+    for (int r = 0; r < R; ++r) live += shade_slot<BVH, F32HIT>(P, base + r * stride, exact, mat, aux, npix, total_items);
 #ifdef RTW_CTA_SYNC
     // CTA-wide barrier + vote: the warps of a CTA walk the sphere rows in step (one stream of
     // constant-cache lines per CTA instead of one per warp)
@@ -730,11 +788,11 @@ cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_c
 
 template <int R, int G>
 static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots, const ConstRows &cr,
-                                  bool crows, bool in_smem, bool bvh, size_t smem, int sm_count,
-                                  int *grid_out, cudaStream_t st) {
-#define RTW_FUSED(CR_, SM_, BV_)                                                                   \
+                                  bool crows, bool in_smem, bool bvh, bool f32hit, size_t smem,
+                                  int sm_count, int *grid_out, cudaStream_t st) {
+#define RTW_FUSED(CR_, SM_, BV_, ...)                                                              \
   do {                                                                                             \
-    auto k = fused_kernel<R, G, CR_, SM_, BV_>;                                                         \
+    auto k = fused_kernel<R, G, CR_, SM_, BV_, ##__VA_ARGS__>;                                     \
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return e;                                                                \
     int per_sm = 0;                                                                                \
@@ -749,7 +807,9 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
     *grid_out = grid;                                                                              \
     k<<<grid, kWBlock, smem, st>>>(p, cr);                                                         \
   } while (0)
-  if (bvh && in_smem) RTW_FUSED(false, true, true);
+  if (f32hit && crows && in_smem) RTW_FUSED(true, true, false, true);
+  else if (f32hit) RTW_FUSED(false, false, false, true);
+  else if (bvh && in_smem) RTW_FUSED(false, true, true);
   else if (bvh) RTW_FUSED(false, false, true);
   else if (crows && in_smem) RTW_FUSED(true, true, false);
   else if (crows) RTW_FUSED(true, false, false);
@@ -760,9 +820,10 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
 }
 
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
-                      bool use_bvh, int sm_count, size_t smem_optin_max, cudaStream_t st,
+                      bool use_bvh, bool f32_hit, int sm_count, size_t smem_optin_max, cudaStream_t st,
                       WaveRunInfo *info) {
   if (use_bvh && !p.scene.bvh_nodes) return cudaErrorInvalidValue;
+  if (use_bvh && f32_hit) return cudaErrorInvalidValue;
   static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
   const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
                      !getenv("RT_B200_NO_CONST_ROWS");
@@ -774,8 +835,8 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
   const bool in_smem = (scene_smem + 1024) * RTW_MINB <= smem_optin_max;
   const size_t smem = in_smem ? scene_smem : 0;
   int grid = 0;
-  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, smem, sm_count, &grid, st)
-                           : launch_fused_t<2, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, smem, sm_count, &grid, st);
+  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st)
+                           : launch_fused_t<2, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st);
   const uint32_t n_slots = p.n_slots;
   if (info) {
     info->launches = 1; info->waves = 0; info->n_slots = n_slots; info->rays_per_lane = rpl;

@@ -112,17 +112,22 @@ def primary_hits(spheres: np.ndarray, cam: OrcCamera, W: int, H: int):
     return ids, t, nrm, ff
 
 
+MODEL_CPU, MODEL_GPU = 0, 1  # src/cpu (spec) | src/gpu (v4 book) semantics
+
+
 def render(spheres: np.ndarray, cam: OrcCamera, W: int, H: int, spp: int, depth: int = 50,
            mode: int = RNG_PHILOX, seed: int = 0, sample_offset: int = 0, ctx: Ctx | None = None,
-           rows=None):
+           rows=None, model: int = MODEL_CPU):
     """-> (linear f64 sums [rows][W][3], samples, rays)"""
     spheres = np.ascontiguousarray(spheres, np.float64)
+    lib().orc_set_model(model)
     r0, r1 = rows if rows is not None else (0, H)
     lin = np.zeros((r1 - r0, W, 3))
     st = (C.c_uint64 * 2)()
     lib().orc_render(ctx.h if ctx is not None else None, spheres.ctypes.data, len(spheres),
                      C.byref(cam), W, H, spp, depth, mode, seed, sample_offset, r0, r1,
                      lin.ctypes.data, st)
+    lib().orc_set_model(MODEL_CPU)
     return lin, int(st[0]), int(st[1])
 
 
@@ -143,3 +148,15 @@ def philox(ctr, key):
     o = (C.c_uint32 * 4)()
     lib().orc_philox4x32_10(c, k, o)
     return list(o)
+
+
+def closest_hit(spheres: np.ndarray, org, dirv, t_min=0.001, t_max=float("inf"), model: int = MODEL_CPU):
+    """hittable_list::hit over the rows in insertion order -> (sphere index or -1, t)"""
+    spheres = np.ascontiguousarray(spheres, np.float64)
+    t = C.c_double(0.0)
+    d3 = lambda a: (C.c_double * 3)(*a)
+    lib().orc_set_model(model)
+    idx = lib().orc_closest_hit(spheres.ctypes.data, len(spheres), d3(org), d3(dirv), t_min, t_max,
+                                C.byref(t), None, None, None)
+    lib().orc_set_model(MODEL_CPU)
+    return idx, t.value

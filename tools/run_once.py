@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--ppm", default=None)
     ap.add_argument("--slices", default=None, help="a:b = render only canonical slices [a,b) (one rank's share)")
     ap.add_argument("--bvh", action="store_true", help="closest hit through the host-built BVH")
+    ap.add_argument("--flags", type=int, default=0, help="extra RT_FLAG_* bits (16 = v4 model, 32 = f32 hit)")
     ap.add_argument("--rows", default=None, help="scene dump file (f64 [n][9]) instead of a golden scene")
     ap.add_argument("--nspheres", type=int, default=0, help="truncate / tile the scene to n spheres (timing experiments)")
     a = ap.parse_args()
@@ -51,7 +52,7 @@ def main():
     scene = rt.Scene(rows)
     frame = rt.Frame(a.w, a.h)
     sb, se = (int(x) for x in a.slices.split(":")) if a.slices else (0, rt.SLICES)
-    cfg = rt.Config(a.w, a.h, a.spp, a.depth, seed=a.seed, flags=rt.FLAG_BVH if a.bvh else 0,
+    cfg = rt.Config(a.w, a.h, a.spp, a.depth, seed=a.seed, flags=(rt.FLAG_BVH if a.bvh else 0) | a.flags,
                     slice_begin=sb, slice_end=se)
     for _ in range(a.reps):
         st = frame.render(scene, cam, cfg)
