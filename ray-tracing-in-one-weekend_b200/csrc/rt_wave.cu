@@ -159,13 +159,20 @@ __device__ __forceinline__ double wave_dsqrt(double x) {  // see rt_path.cu fast
 
 struct WRay {
   double ox, oy, oz, dx, dy, dz, a, tminA;
+  double lo;  // smallest acceptable root numerator: tminA, or the next double above it when strict
 };
+__device__ __forceinline__ double next_up_pos(double x) {  // x > 0 finite
+  return __longlong_as_double(__double_as_longlong(x) + 1ll);
+}
 
 // sphere::hit on numerators (root = N / a, a common to the ray): src/cpu/sphere.h:24-51 with the
-// inclusive upper bound of hittable_list.h:34-39 (a later sphere with an equal root wins).
-// strict = the v4 interval of src/gpu/sphere.h:31-36 (t_min < root < t_max: the earlier sphere wins).
+// inclusive upper bound of hittable_list.h:34-39 (a later sphere with an equal root wins), or —
+// strict — the v4 interval of src/gpu/sphere.h:31-36 (t_min < root < t_max: the earlier sphere
+// wins).  Both are ONE pair of compares, N < lo || !(N < hi): the bounds carry the rule
+// (lo = t_min or the next double above it; hi = the best root, or the next double above it when
+// an equal root may replace it).
 __device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, double &bestN,
-                                               const bool strict) {
+                                               double &hi, const bool strict) {
   double ocx = r.ox - S.x, ocy = r.oy - S.y, ocz = r.oz - S.z;
   double half_b = ocx * r.dx + ocy * r.dy + ocz * r.dz;
   double c = ocx * ocx + ocy * ocy + ocz * ocz - S.w * S.w;
@@ -173,11 +180,12 @@ __device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, d
   if (disc < 0.0) return false;
   double sq = wave_dsqrt(disc);
   double N = -half_b - sq;
-  if (strict ? (N <= r.tminA || bestN <= N) : (N < r.tminA || bestN < N)) {
+  if (N < r.lo || !(N < hi)) {
     N = -half_b + sq;
-    if (strict ? (N <= r.tminA || bestN <= N) : (N < r.tminA || bestN < N)) return false;
+    if (N < r.lo || !(N < hi)) return false;
   }
   bestN = N;
+  hi = strict ? N : next_up_pos(N);
   return true;
 }
 
@@ -210,6 +218,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
     ray.a = ray.dx * ray.dx + ray.dy * ray.dy + ray.dz * ray.dz;
     ray.tminA = 0.001 * (double)RO.w * ray.a;  // main.cc:19 t_min in unit-direction units, times a
     double bestN = __longlong_as_double(0x7ff0000000000000ll);
+    double hi = bestN;
     if (BVH) {
       // the traversal already resolved the closest hit: {id, numerator of the root}
       id = (int)P.cand_idx[i];
@@ -232,10 +241,10 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
         const float c = ocx * ocx + ocy * ocy + ocz * ocz - r * r;
         const float disc = hb * hb - a * c;
         if (disc < 0.0f) return;
-        const float sq = sqrtf(disc);
-        float root = (-hb - sq) / a;
+        const float sq = __fsqrt_rn(disc);  // IEEE like the reference's build (this TU uses approximate / and sqrt)
+        float root = __fdiv_rn(-hb - sq, a);
         if (strict ? !(0.001f < root && root < bestT) : (root < 0.001f || bestT < root)) {
-          root = (-hb + sq) / a;
+          root = __fdiv_rn(-hb + sq, a);
           if (strict ? !(0.001f < root && root < bestT) : (root < 0.001f || bestT < root)) return;
         }
         bestT = root;
@@ -263,6 +272,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
     } else {
       const uint32_t cnt = P.cand_cnt[i];
       const bool strict = P.model_v4 != 0u;
+      ray.lo = strict ? next_up_pos(ray.tminA) : ray.tminA;
       const uint32_t skip = (uint32_t)__float_as_int(RD.w);  // the sphere the ray just left, or -1
       if (cnt <= kCandPlanes) {
         // entries {first row of a group << kCandShift | mask of its rows that passed}, ascending;
@@ -278,11 +288,11 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
           }
           const uint32_t s = s0 + (uint32_t)__ffs((int)m) - 1u;
           m &= m - 1u;
-          if (s != skip && wave_exact_hit(exact[s], ray, bestN, strict)) id = (int)s;
+          if (s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
         }
       } else {  // candidate planes overflowed: exact test of every sphere (rare)
         for (uint32_t s = 0; s < P.scene.n; ++s)
-          if (s != skip && wave_exact_hit(exact[s], ray, bestN, strict)) id = (int)s;
+          if (s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
       }
     }
     if (id < 0) {
