@@ -48,25 +48,25 @@ struct CameraF64 {
 
 // ---------------------------------------------------------------- canonical sample slices
 // The spp samples of a pixel are cut into 64 canonical slices in 8 blocks of 8.  Block b covers
-// [floor(b*spp/8), floor((b+1)*spp/8)); inside a block slices 0..3 each take half (rounded up) of
-// what the slices before them left, and slices 4..7 share the remaining sixteenth evenly
-// (31, 16, 8, 4, 1, 1, 1, 0 for 62 samples; 256, 128, 64, 32, 8, 8, 8, 8 for 512).  Work items
-// are handed out largest slices first, so a frame ends on its smallest items and the
-// end-of-frame tail stays short however few slices a GPU owns.
+// [floor(b*spp/8), floor((b+1)*spp/8)); inside a block the slices take 13, 12, 10, 9, 8, 6, 3, 1
+// sixty-secondths of it (exactly those sample counts at 500 spp, where a block has 62 samples).
+// Work items are handed out largest slices first, so a frame ends on its smallest items; and the
+// largest item stays below a fifth of a block — with one block per GPU (8 GPUs) an item of a
+// pixel that needs ~25 ray segments per sample must still be much shorter than the whole kernel
+// (a bounce costs one pass over the spheres, ~36 us: halving sizes 31, 16, 8... put single items
+// of the glass-ball pixels on the critical path: 31 x 23 x 36 us = 26 ms in a 21 ms kernel).
 __host__ __device__ __forceinline__ void slice_range(uint32_t k, uint32_t spp, uint32_t &begin,
                                                      uint32_t &end) {
   const uint32_t blk = k >> 3, j = k & 7u;
-  uint32_t lo = (uint32_t)(((uint64_t)blk * spp) >> 3);
+  const uint32_t lo = (uint32_t)(((uint64_t)blk * spp) >> 3);
   const uint32_t hi = (uint32_t)(((uint64_t)(blk + 1) * spp) >> 3);
-  for (uint32_t i = 0; i < (j < 4u ? j : 4u); ++i) lo += (hi - lo + 1u) >> 1;
-  if (j < 4u) {
-    begin = lo;
-    end = lo + ((hi - lo + 1u) >> 1);
-  } else {
-    const uint32_t rest = hi - lo, q = j - 4u;  // quarter q of the rest, earlier quarters larger
-    begin = lo + (uint32_t)(((uint64_t)q * rest + 3u) >> 2);
-    end = lo + (uint32_t)(((uint64_t)(q + 1u) * rest + 3u) >> 2);
-  }
+  // cumulative weights 0, 13, 25, 35, 44, 52, 58, 61, 62 packed one byte each
+  const uint64_t cum = 0x3e3d3a342c23190dull;  // bytes: 13, 25, 35, 44, 52, 58, 61, 62
+  const uint32_t c0 = j ? (uint32_t)(cum >> (8u * (j - 1u))) & 0xffu : 0u;
+  const uint32_t c1 = (uint32_t)(cum >> (8u * j)) & 0xffu;
+  const uint32_t n = hi - lo;
+  begin = lo + (uint32_t)(((uint64_t)n * c0) / 62u);
+  end = lo + (uint32_t)(((uint64_t)n * c1) / 62u);
 }
 // order_idx-th slice of the aligned block [sb, se) in hand-out order (big slices first)
 __host__ __device__ __forceinline__ uint32_t slice_in_order(uint32_t order_idx, uint32_t sb, uint32_t se) {

@@ -13,6 +13,7 @@
 //    Survivors (a handful per ray) are pushed to a per-lane candidate list and resolved in
 //    f64 with exactly the reference's sphere::hit arithmetic, so closest-hit decisions do
 //    not suffer f32 cancellation (r = 1000 ground sphere).
+#include <cstdlib>
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
@@ -240,7 +241,9 @@ cudaError_t launch_cost_order(const float4 *partial, uint32_t npix, float inv_sa
   if (e != cudaSuccess) return e;
   // pixels whose paths are long on average (glass, facing mirrors) are where the rare 50-bounce
   // paths live: ALL their slices are handed out before anything else
-  heavy_count_kernel<<<1, 1, 0, st>>>(keys_out, npix, 255u - 4u * kHeavyRays, heavy);
+  unsigned quarter_rays = 4u * kHeavyRays;
+  if (const char *e = getenv("RT_B200_HEAVY_QUARTER_RAYS")) quarter_rays = (unsigned)atoi(e);  // tuning knob
+  heavy_count_kernel<<<1, 1, 0, st>>>(keys_out, npix, 255u - quarter_rays, heavy);
   return cudaGetLastError();
 }
 

@@ -329,7 +329,25 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       // hand-out order: first every slice of the heavy pixels, then the other pixels slice by
       // slice (largest slices first, heaviest pixels first within a slice)
       uint32_t ord, px;
-      if (P.order) {
+      if (total_items <= 0xffffffffull) {
+        // 32-bit arithmetic (a 64-bit division is ~100 instructions at a few active lanes)
+        const uint32_t q32 = (uint32_t)itq;
+        if (P.order) {
+          const uint32_t nh = __ldg(P.heavy);
+          const uint32_t heavy_items = nh * P.n_orders;
+          if (q32 < heavy_items) {
+            ord = q32 / nh;
+            px = __ldg(P.order + (q32 - ord * nh));
+          } else {
+            const uint32_t q = q32 - heavy_items, nl = npix - nh;
+            ord = q / nl;
+            px = __ldg(P.order + nh + (q - ord * nl));
+          }
+        } else {
+          ord = q32 / npix;
+          px = q32 - ord * npix;
+        }
+      } else if (P.order) {
         const uint32_t nh = __ldg(P.heavy);
         const uint64_t heavy_items = (uint64_t)nh * P.n_orders;
         if (itq < heavy_items) {

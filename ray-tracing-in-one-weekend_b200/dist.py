@@ -31,20 +31,18 @@ def slice_block(rank: int, world: int) -> tuple[int, int]:
     return rank * per, (rank + 1) * per
 
 
+SLICE_CUM = (0, 13, 25, 35, 44, 52, 58, 61, 62)  # cumulative slice weights inside a block
+
+
 def slice_samples(k: int, spp: int) -> tuple[int, int]:
     """Frame-relative sample range [begin, end) of canonical slice k — the same rule as
     slice_range() in csrc/rt_device.cuh: 8 blocks of 8 slices; block b covers
-    [floor(b*spp/8), floor((b+1)*spp/8)); inside a block slices 0..3 each take half (rounded up)
-    of what is left, slices 4..7 share the remaining sixteenth evenly
-    (31, 16, 8, 4, 1, 1, 1, 0 for 62 samples)."""
+    [floor(b*spp/8), floor((b+1)*spp/8)); inside a block the slices take 13, 12, 10, 9, 8, 6, 3, 1
+    sixty-secondths (exactly those counts for a 62-sample block, i.e. at 500 spp)."""
     blk, j = divmod(k, 8)
     lo, hi = (blk * spp) // 8, ((blk + 1) * spp) // 8
-    for _ in range(min(j, 4)):
-        lo += (hi - lo + 1) // 2
-    if j < 4:
-        return lo, lo + (hi - lo + 1) // 2
-    rest, q = hi - lo, j - 4
-    return lo + (q * rest + 3) // 4, lo + ((q + 1) * rest + 3) // 4
+    n = hi - lo
+    return lo + n * SLICE_CUM[j] // 62, lo + n * SLICE_CUM[j + 1] // 62
 
 
 def samples_of_block(begin: int, end: int, spp: int) -> int:
