@@ -1,6 +1,6 @@
 // csrc/rt_kernels.cu — hand-written sm_100a kernels of the path-tracing hot path.
 //
-//   (the persistent path-tracing megakernel lives in rt_path.cu)
+//   (the persistent path-tracing kernel lives in rt_wave.cu)
 //   reduce_local      canonical pairwise tree over the slices one GPU rendered.
 //   finalize_kernel   upper tree levels over per-GPU partials + write_color (color.h:8-23).
 //   primary_f32       production-precision primary-hit table (accuracy gate, f32 leg).

@@ -1,21 +1,24 @@
-// csrc/rt_wave.cu — wavefront form of the path-tracing hot path (sm_100a).
+// csrc/rt_wave.cu — the path-tracing hot path (sm_100a): everything executed per (pixel, sample)
+// of src/cpu/main.cc:111-123.
 //
-// The same arithmetic as the megakernel in rt_path.cu, cut into two kernels that alternate
-// over a pool of path slots resident in HBM/L2:
+// Path state lives in a pool of slots in device memory (L2-resident); two device functions
+// alternate over it:
 //
-//   shade_kernel   one lane = one slot.  Finishes the ray segment traced in the previous wave:
-//                  f64 resolution of the filter's candidates (sphere::hit, src/cpu/sphere.h:24-51),
-//                  sky or material scatter (main.cc:12-30, material.h), then, if the path ended,
-//                  path regeneration: next sample of the slot's (pixel, slice) item or the next
-//                  item of the frame's work queue, camera::get_ray (camera.h:28-35).
-//   filter_kernel  one lane = R slots.  Conservative f32 line-sphere test of R rays against ALL
+//   shade_slot     one slot.  Finishes the ray segment traced by the previous pass: f64 resolution
+//                  of the filter's candidates (sphere::hit, src/cpu/sphere.h:24-51), sky or material
+//                  scatter (main.cc:12-30, material.h), then, if the path ended, path regeneration:
+//                  next sample of the slot's (pixel, slice) item or the next item of the frame's
+//                  work queue, camera::get_ray (camera.h:28-35).
+//   filter_rays    R slots of one lane.  Conservative f32 line-sphere test of R rays against ALL
 //                  spheres in reference order (hittable_list::hit visits every object,
 //                  hittable_list.h:28-43): packed FFMA2, sphere rows through the constant bank
-//                  into uniform registers.  Survivors are appended to the slot's candidate
-//                  planes in ascending sphere order.  The lane carries no path state, only rays.
+//                  into uniform registers.  Survivors are recorded as {group, row mask} entries in
+//                  the slot's candidate planes.  The lane carries no path state, only rays.
+//   bvh_trace      optional replacement of filter_rays: closest hit through the host-built BVH.
 //
-// The filter kernel is >85 % of the frame and nothing but the loop; the divergent, latency-bound
-// code (RNG, materials, f64) runs one slot per lane at full occupancy in the shade kernel.
+// fused_kernel is the product: a persistent kernel in which every lane owns R slots for the whole
+// frame and alternates the two phases.  shade_kernel / filter_kernel run the same functions as a
+// two-kernel wavefront (A/B variant, RT_FLAG_WAVEFRONT).
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
@@ -147,7 +150,8 @@ filter_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Cons
 }
 
 // ================================================================ shade
-__device__ __forceinline__ double wave_dsqrt(double x) {  // see rt_path.cu fast_dsqrt
+// sqrt of a non-negative double: rsqrt seed in f32, two Newton steps in f64 (no f64 division)
+__device__ __forceinline__ double wave_dsqrt(double x) {
   float xf = fmaxf((float)x, 1e-30f);
   double y = (double)rsqrtf(xf);
   double h = 0.5 * y;
