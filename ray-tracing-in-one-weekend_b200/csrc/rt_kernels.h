@@ -27,7 +27,7 @@ struct ConstRows {
 };
 
 // ---------------------------------------------------------------- wavefront form (rt_wave.cu)
-constexpr unsigned kCandPlanes = 16;  // candidate entries kept per ray before the exact full scan
+constexpr unsigned kCandPlanes = 32;  // candidate entries kept per ray before the full scan of shade_slot
 constexpr unsigned kCandShift = 8;    // entry = first row of a decision group << kCandShift | row mask
 
 struct WaveParams {

@@ -294,9 +294,19 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
           m &= m - 1u;
           if (s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
         }
-      } else {  // candidate planes overflowed: exact test of every sphere (rare)
-        for (uint32_t s = 0; s < P.scene.n; ++s)
-          if (s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
+      } else {
+        // candidate planes overflowed (a ray along a long row of spheres): scan every sphere, the
+        // same conservative f32 test first so that f64 work is spent on its survivors only
+        const float nod = -(RO.x * RD.x + RO.y * RD.y + RO.z * RD.z);
+        const float ox2 = 2.0f * RO.x, oy2 = 2.0f * RO.y, oz2 = 2.0f * RO.z;
+        const float oot = (RO.x * RO.x + RO.y * RO.y + RO.z * RO.z) * (1.0f - RTB_FILTER_SLACK);
+        const float4 *fast = P.scene.fast;
+        for (uint32_t s = 0; s < P.scene.n; ++s) {
+          const float4 S = __ldg(fast + s);
+          const float b = fmaf(S.x, RD.x, fmaf(S.y, RD.y, fmaf(S.z, RD.z, nod)));
+          const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
+          if (e >= oot && s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
+        }
       }
     }
     if (id < 0) {

@@ -72,7 +72,7 @@ def test_bounce_limit(rt, orc, depth):
 
 def test_candidate_overflow_falls_back_to_the_full_scan(rt, orc):
     """A ray down a row of 150 glass beads passes the f32 filter for every one of them: more than
-    the 16 candidate entries a slot holds, so the shade pass must test every sphere exactly."""
+    the 32 candidate entries a slot holds, so the shade pass must test every sphere exactly."""
     W, H, spp = 32, 18, 4
     n = 150
     rows = np.zeros((n + 1, 9))
