@@ -15,7 +15,10 @@ constexpr unsigned kItemPixelMask = (1u << kItemShift) - 1u;
 
 // Scene rows are padded to a multiple of kRowPad (padding rows never pass the filter) and the
 // filter-row array carries kRowTail more padding rows for the loop's prefetch.
-constexpr unsigned kRowPad = 8, kRowTail = 8;
+#ifndef RTW_G
+#define RTW_G 4  // sphere rows per decision group of the filter loop (two groups per trip)
+#endif
+constexpr unsigned kRowPad = 2 * RTW_G, kRowTail = 2 * RTW_G;
 
 namespace rtb {
 

@@ -786,8 +786,8 @@ cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_c
     return cudaGetLastError();
   };
   auto filter = [&]() -> cudaError_t {
-    return rpl == 4 ? launch_filter_t<4, 4>(p, cr, crows, filter_grid, st)
-                    : launch_filter_t<2, 4>(p, cr, crows, filter_grid, st);
+    return rpl == 4 ? launch_filter_t<4, RTW_G>(p, cr, crows, filter_grid, st)
+                    : launch_filter_t<2, RTW_G>(p, cr, crows, filter_grid, st);
   };
 
   uint32_t launches = 0, waves = 0;
@@ -877,8 +877,8 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
   const bool in_smem = (scene_smem + 1024) * RTW_MINB <= smem_optin_max;
   const size_t smem = in_smem ? scene_smem : 0;
   int grid = 0;
-  cudaError_t e = rpl == 4 ? launch_fused_t<4, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st)
-                           : launch_fused_t<2, 4>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st);
+  cudaError_t e = rpl == 4 ? launch_fused_t<4, RTW_G>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st)
+                           : launch_fused_t<2, RTW_G>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st);
   const uint32_t n_slots = p.n_slots;
   if (info) {
     info->launches = 1; info->waves = 0; info->n_slots = n_slots; info->rays_per_lane = rpl;
