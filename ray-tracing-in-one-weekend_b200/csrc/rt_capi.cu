@@ -71,6 +71,7 @@ struct rt_frame {
   void *sort_temp;
   size_t sort_temp_bytes;
   bool order_valid;
+  bool order_heavy_only;    // the order was made for BVH frames (heavy pixels first, the rest in scan order)
 };
 
 extern "C" const char *rt_last_error(void) { return g_err; }
@@ -342,7 +343,8 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
   w.seed = cfg->seed; w.sample_offset = cfg->sample_offset;
   w.slice_begin = cfg->slice_begin; w.slice_end = cfg->slice_end;
   w.accum = f->accum; w.counter = f->counters;
-  w.order = f->order_valid && !getenv("RT_B200_NO_COST_ORDER") ? f->order : nullptr;
+  const bool bvh_frame = (cfg->flags & RT_FLAG_BVH) != 0;
+  w.order = f->order_valid && f->order_heavy_only == bvh_frame && !getenv("RT_B200_NO_COST_ORDER") ? f->order : nullptr;
   w.heavy = f->heavy;
   f->last_n = sc->n;
   // hand-out order = largest slices first; trailing slices without samples are not queued
@@ -428,9 +430,10 @@ extern "C" int rt_frame_reduce_local(rt_frame *f, const rt_config *cfg) {
   }
   if (own) {
     CU(launch_cost_order(f->partial, f->npix, 1.0f / (float)own, f->sort_keys, f->sort_keys_out,
-                         f->sort_iota, f->order, f->heavy, f->sort_temp, f->sort_temp_bytes, f->sm_count,
-                         f->stream));
+                         f->sort_iota, f->order, f->heavy, (cfg->flags & RT_FLAG_BVH) != 0, f->sort_temp,
+                         f->sort_temp_bytes, f->sm_count, f->stream));
     f->order_valid = true;
+    f->order_heavy_only = (cfg->flags & RT_FLAG_BVH) != 0;
   }
   CU(cudaStreamSynchronize(f->stream));
   return RT_OK;

@@ -199,14 +199,16 @@ cudaError_t launch_ffma_peak(float *out, int blocks, int iters, long long *cycle
 // the work queue runs dry are the cheap ones and the end-of-frame tail is short.  The order only
 // schedules work: every item's sum is independent of it, and so is the image.
 __global__ void __launch_bounds__(256) cost_keys_kernel(const float4 *__restrict__ partial, uint32_t npix,
-                                                        float inv_samples, uint32_t *__restrict__ keys,
+                                                        float inv_samples, uint32_t heavy_quarter_rays,
+                                                        bool heavy_only, uint32_t *__restrict__ keys,
                                                         uint32_t *__restrict__ iota) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
     // quarter-ray resolution, 8-bit key, ascending key = descending cost; the sort is stable, so
-    // pixels of equal cost keep their scan order (coherent neighbours stay neighbours)
+    // pixels of equal cost keep their scan order (coherent neighbours stay neighbours).
+    // heavy_only: two keys -- the heavy pixels, then everything else in scan order
     const float q = __ldg(&partial[i]).w * inv_samples * 4.0f;
     const uint32_t c = q >= 255.0f ? 255u : (uint32_t)q;
-    keys[i] = 255u - c;
+    keys[i] = heavy_only ? (c >= heavy_quarter_rays ? 0u : 1u) : 255u - c;
     iota[i] = i;
   }
 }
@@ -232,18 +234,20 @@ size_t cost_order_temp_bytes(uint32_t npix) {
 
 cudaError_t launch_cost_order(const float4 *partial, uint32_t npix, float inv_samples, uint32_t *keys,
                               uint32_t *keys_out, uint32_t *iota, uint32_t *order, uint32_t *heavy,
-                              void *temp, size_t temp_bytes, int sm_count, cudaStream_t st) {
+                              bool heavy_only, void *temp, size_t temp_bytes, int sm_count,
+                              cudaStream_t st) {
   int grid = sm_count * 8;
-  cost_keys_kernel<<<grid, 256, 0, st>>>(partial, npix, inv_samples, keys, iota);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys, keys_out, iota, order, (int)npix, 0, 8, st);
-  if (e != cudaSuccess) return e;
   // pixels whose paths are long on average (glass, facing mirrors) are where the rare 50-bounce
   // paths live: ALL their slices are handed out before anything else
   unsigned quarter_rays = 4u * kHeavyRays;
   if (const char *e = getenv("RT_B200_HEAVY_QUARTER_RAYS")) quarter_rays = (unsigned)atoi(e);  // tuning knob
-  heavy_count_kernel<<<1, 1, 0, st>>>(keys_out, npix, 255u - quarter_rays, heavy);
+  if (quarter_rays > 255u) quarter_rays = 255u;
+  cost_keys_kernel<<<grid, 256, 0, st>>>(partial, npix, inv_samples, quarter_rays, heavy_only, keys, iota);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys, keys_out, iota, order, (int)npix, 0, 8, st);
+  if (e != cudaSuccess) return e;
+  heavy_count_kernel<<<1, 1, 0, st>>>(keys_out, npix, heavy_only ? 0u : 255u - quarter_rays, heavy);
   return cudaGetLastError();
 }
 

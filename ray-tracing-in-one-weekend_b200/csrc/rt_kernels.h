@@ -86,11 +86,14 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
                       WaveRunInfo *info);
 
 // Pixel hand-out order by descending cost (ray segments per sample in `partial`), stable.
+// heavy_only: only the heavy pixels move to the front, the others keep their scan order (BVH
+// mode: neighbouring lanes then trace neighbouring pixels, and coherent rays share nodes).
 size_t cost_order_temp_bytes(uint32_t npix);
 constexpr unsigned kHeavyRays = 5;  // rays per sample from which a pixel counts as "heavy"
 cudaError_t launch_cost_order(const float4 *partial, uint32_t npix, float inv_samples, uint32_t *keys,
                               uint32_t *keys_out, uint32_t *iota, uint32_t *order, uint32_t *heavy,
-                              void *temp, size_t temp_bytes, int sm_count, cudaStream_t st);
+                              bool heavy_only, void *temp, size_t temp_bytes, int sm_count,
+                              cudaStream_t st);
 
 // dst[i] = canonical sub-tree sum of slices [slice_begin, slice_end) (aligned power of 2).
 cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t slice_begin,

@@ -670,8 +670,11 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
 // loop, state in the pool) and filter (R rays at once, registers hold nothing but rays).  No
 // kernel boundary, no inter-lane dependency; warps of an SM drift apart, so the latency-bound
 // shade phases of some warps overlap the FMA-pipe-bound filter phases of the others.
+// CTAs per SM: the brute-force form needs its 78 registers (3 x 256 threads); the BVH form fits 64
+// and is bound by load latency, so it takes a fourth CTA.
+constexpr int kBvhMinB = RTW_MINB + 1;
 template <int R, int G, bool CROWS, bool SMEM, bool BVH, bool F32HIT = false>
-__global__ void __launch_bounds__(kWBlock, RTW_MINB)
+__global__ void __launch_bounds__(kWBlock, BVH ? kBvhMinB : RTW_MINB)
 fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t s_bar;
@@ -842,7 +845,9 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
     if (e != cudaSuccess) return e;                                                                \
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;                                          \
     /* persistent grid: every CTA must be resident (one full wave, a multiple of the SM count) */  \
-    const int grid = sm_count * (per_sm < RTW_MINB ? per_sm : RTW_MINB);                           \
+    int want = BV_ ? kBvhMinB : RTW_MINB;                                                          \
+    while (want > 1 && (size_t)sm_count * want * kWBlock * R > pool_slots) --want;                 \
+    const int grid = sm_count * (per_sm < want ? per_sm : want);                                   \
     const uint32_t n_slots = (uint32_t)grid * kWBlock * (uint32_t)R;                               \
     if (n_slots > pool_slots) return cudaErrorInvalidValue;                                        \
     wave_carve(p, pool, n_slots);                                                                  \
