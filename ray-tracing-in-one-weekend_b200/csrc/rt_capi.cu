@@ -34,6 +34,17 @@ static int fail(int code, const char *fmt, ...) {
                   cudaGetErrorString(e__), __FILE__, __LINE__, #expr);                   \
   } while (0)
 
+// CU for the create functions: the half-built object is destroyed before the error is returned
+#define CU_OR(cleanup, expr)                                                             \
+  do {                                                                                   \
+    cudaError_t e__ = (expr);                                                            \
+    if (e__ != cudaSuccess) {                                                            \
+      cleanup;                                                                           \
+      return fail(RT_E_CUDA, "CUDA error %d (%s) at %s:%d '%s'", (int)e__,               \
+                  cudaGetErrorString(e__), __FILE__, __LINE__, #expr);                   \
+    }                                                                                    \
+  } while (0)
+
 struct rt_scene {
   int device;
   uint32_t n;
@@ -138,10 +149,10 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
     rt_scene_destroy(sc);
     return fail(RT_E_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
   }
-  CU(cudaMemcpy(sc->fast, fast.data(), (m + kRowTail) * sizeof(float4), cudaMemcpyHostToDevice));
-  CU(cudaMemcpy(sc->exact, exact.data(), m * sizeof(double4), cudaMemcpyHostToDevice));
-  CU(cudaMemcpy(sc->mat, mat.data(), m * sizeof(float4), cudaMemcpyHostToDevice));
-  CU(cudaMemcpy(sc->aux, aux.data(), m * sizeof(float2), cudaMemcpyHostToDevice));
+  CU_OR(rt_scene_destroy(sc), cudaMemcpy(sc->fast, fast.data(), (m + kRowTail) * sizeof(float4), cudaMemcpyHostToDevice));
+  CU_OR(rt_scene_destroy(sc), cudaMemcpy(sc->exact, exact.data(), m * sizeof(double4), cudaMemcpyHostToDevice));
+  CU_OR(rt_scene_destroy(sc), cudaMemcpy(sc->mat, mat.data(), m * sizeof(float4), cudaMemcpyHostToDevice));
+  CU_OR(rt_scene_destroy(sc), cudaMemcpy(sc->aux, aux.data(), m * sizeof(float2), cudaMemcpyHostToDevice));
   sc->host_fast = fast;
   {
     // the north-star's optional BVH: built here on the host, used when a render asks for it
@@ -155,8 +166,8 @@ extern "C" int rt_scene_create(const rt_sphere *sp, uint32_t n, int32_t device, 
       rt_scene_destroy(sc);
       return fail(RT_E_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
     }
-    CU(cudaMemcpy(sc->bvh_nodes, nodes.data(), nodes.size() * sizeof(BvhNode), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(sc->bvh_prim, prim.data(), prim.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CU_OR(rt_scene_destroy(sc), cudaMemcpy(sc->bvh_nodes, nodes.data(), nodes.size() * sizeof(BvhNode), cudaMemcpyHostToDevice));
+    CU_OR(rt_scene_destroy(sc), cudaMemcpy(sc->bvh_prim, prim.data(), prim.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   }
   *out = sc;
   return RT_OK;
@@ -250,10 +261,11 @@ extern "C" int rt_frame_create(uint32_t width, uint32_t height, int32_t device, 
   if (!f) return fail(RT_E_NOMEM, "out of host memory");
   memset(f, 0, sizeof *f);
   f->device = device; f->w = width; f->h = height; f->npix = width * height;
-  cudaDeviceProp prop;
-  CU(cudaGetDeviceProperties(&prop, device));
-  f->sm_count = prop.multiProcessorCount;
-  f->smem_optin = prop.sharedMemPerBlockOptin;
+  int sm_count = 0, smem_optin = 0;
+  CU_OR(delete f, cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+  CU_OR(delete f, cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+  f->sm_count = sm_count;
+  f->smem_optin = (size_t)smem_optin;
   size_t quads = (f->npix + 3) / 4;
   cudaError_t e;
   if ((e = cudaMalloc(&f->accum, (size_t)RT_SLICES * f->npix * sizeof(float4))) != cudaSuccess ||
@@ -266,7 +278,7 @@ extern "C" int rt_frame_create(uint32_t width, uint32_t height, int32_t device, 
     return fail(RT_E_CUDA, "frame allocation failed: %s", cudaGetErrorString(e));
   }
   f->stream = f->own_stream;
-  for (int k = 0; k < 4; ++k) CU(cudaEventCreate(&f->ev[k]));
+  for (int k = 0; k < 4; ++k) CU_OR(rt_frame_destroy(f), cudaEventCreate(&f->ev[k]));
   *out = f;
   return RT_OK;
 }
