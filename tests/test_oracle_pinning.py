@@ -97,3 +97,27 @@ def test_live_reference_other_size(orc):
     lin, _, _ = orc.render(rows, orc.scene_camera("cover", W, H), W, H, spp,
                            mode=orc.RNG_MT19937, ctx=ctx)
     assert np.array_equal(lin, ref)
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/src/cpu-multi-threading/main.cc"),
+                    reason="live reference only exists in the build container")
+def test_mt_program_on_one_thread_is_the_oracle(orc):
+    """The CPU baseline bench.py also times is the reference's cpu_multi_threading_ray_tracer, built
+    by oracle/Makefile with its three workload literals read from the environment.  On ONE thread
+    it visits pixels and samples in src/cpu/main.cc's order, so its P3 output must be the oracle's
+    image byte for byte -- the generated copy changes the workload and nothing else."""
+    odir = os.path.dirname(orc.LIB)
+    subprocess.check_call(["make", "-C", odir, "mt_ref"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    W, spp = 48, 2
+    H = int(W / (16.0 / 9.0))
+    env = dict(os.environ, RT_MT_WIDTH=str(W), RT_MT_SPP=str(spp), RT_MT_THREADS="1")
+    r = subprocess.run([os.path.join(odir, "_ref", "cpu_mt_tracer")], env=env, capture_output=True,
+                       text=True, check=True)
+    tok = r.stdout.split()
+    assert tok[:4] == ["P3", str(W), str(H), "255"]
+    img = np.array(tok[4:], dtype=np.int64).reshape(H, W, 3)
+    assert any(l.startswith("Time Cost (ms)") for l in r.stderr.splitlines())
+    ctx = orc.Ctx()
+    rows = orc.cover_scene(ctx)
+    lin, _, _ = orc.render(rows, orc.scene_camera("cover", W, H), W, H, spp, mode=orc.RNG_MT19937, ctx=ctx)
+    assert np.array_equal(img, orc.write_color(lin.reshape(-1, 3), spp).reshape(H, W, 3))
