@@ -30,7 +30,10 @@ struct ConstRows {
 };
 
 // ---------------------------------------------------------------- wavefront form (rt_wave.cu)
-constexpr unsigned kCandPlanes = 32;  // candidate entries kept per ray before the full scan of shade_slot
+#ifndef RTW_CAND_PLANES
+#define RTW_CAND_PLANES 64
+#endif
+constexpr unsigned kCandPlanes = RTW_CAND_PLANES;  // candidate entries kept per ray before the full scan of shade_slot
 constexpr unsigned kCandShift = 8;    // entry = first row of a decision group << kCandShift | row mask
 
 struct WaveParams {

@@ -71,10 +71,11 @@ def test_bounce_limit(rt, orc, depth):
 
 
 def test_candidate_overflow_falls_back_to_the_full_scan(rt, orc):
-    """A ray down a row of 150 glass beads passes the f32 filter for every one of them: more than
-    the 32 candidate entries a slot holds, so the shade pass must test every sphere exactly."""
+    """A ray down a row of 300 glass beads passes the f32 filter for every one of them: 75 groups,
+    more than the 64 candidate entries a slot holds, so the shade pass must test every sphere
+    exactly."""
     W, H, spp = 32, 18, 4
-    n = 150
+    n = 300
     rows = np.zeros((n + 1, 9))
     rows[0] = [0.0, -1000.5, 0.0, 1000.0, 0, 0.5, 0.5, 0.5, 0.0]
     for k in range(n):
