@@ -30,6 +30,7 @@ extern "C" {
 #define RT_LAMBERTIAN 0u /* src/cpu/material.h:14-34 */
 #define RT_METAL 1u      /* src/cpu/material.h:36-51 */
 #define RT_DIELECTRIC 2u /* src/cpu/material.h:53-87 */
+#define RT_KIND_MAX RT_DIELECTRIC
 
 #define RT_SLICES 64u /* canonical sample slices per pixel (multi-GPU split) */
 
@@ -80,6 +81,11 @@ typedef struct rt_config {
                                  |oc|^2 - r^2 on the r = 1000 ground sphere that darkens the reference CUDA
                                  program's ground; brute-force fused mode only (not with RT_FLAG_BVH /
                                  RT_FLAG_WAVEFRONT). */
+#define RT_FLAG_NO_FILTER 64u /* debug/soundness switch: the f32 line-sphere pre-test of the brute-force scan is
+                                 switched off and every ray resolves EVERY sphere in f64 (hittable_list::hit as
+                                 written, src/cpu/hittable_list.h:28-43).  The image must be byte-identical with
+                                 and without it: that is the test of the filter's conservativeness
+                                 (tests/test_filter_soundness.py).  ~50x slower; brute-force fused mode only. */
 
 typedef struct rt_stats {
   uint64_t samples;      /* samples traced by this call */
@@ -101,10 +107,18 @@ const char *rt_version(void);
 int rt_device_count(int *count);
 
 /* --- scene: replaces hittable_list + sphere + material objects (src/cpu/hittable_list.h,
- *     sphere.h, material.h) and the GPU twin's new_world kernel (src/gpu/main.cu:18-75). */
+ *     sphere.h, material.h) and the GPU twin's new_world kernel (src/gpu/main.cu:18-75).
+ *     One device allocation, one host->device copy from a pinned staging buffer the scene owns.
+ *     The optional BVH is built on the host at the first RT_FLAG_BVH render, not here. */
 int rt_scene_create(const rt_sphere *spheres, uint32_t n, int32_t device, rt_scene **out);
 int rt_scene_destroy(rt_scene *);
 int rt_scene_count(const rt_scene *, uint32_t *n);
+/* Replace the spheres of an existing scene (hittable_list::clear + add, hittable_list.h:17-20) without
+ * re-allocating: n must fit the capacity the scene was created with (its n rounded up to 8).  The
+ * rows are flattened into the scene's pinned staging buffer and copied with ONE cudaMemcpyAsync on
+ * `cuda_stream` (a cudaStream_t; NULL = the default stream, synchronous); renders ordered after it
+ * on the same stream see the new spheres.  This is the per-frame H2D of an animation loop. */
+int rt_scene_update(rt_scene *, const rt_sphere *spheres, uint32_t n, void *cuda_stream);
 
 /* --- frame: accumulation buffers [RT_SLICES][H][W] float4 on the device. */
 int rt_frame_create(uint32_t width, uint32_t height, int32_t device, rt_frame **out);
@@ -114,8 +128,16 @@ int rt_frame_destroy(rt_frame *);
 int rt_frame_partial_ptr(rt_frame *, void **dev_ptr, size_t *bytes);
 
 /* Run the frame's work on a caller-owned CUDA stream (a cudaStream_t; NULL = the frame's own
- * stream) so that collectives and kernels order on one stream. */
+ * stream) so that collectives and kernels order on one stream.  While a caller-owned stream is
+ * set, rt_render, rt_frame_reduce_local and rt_finalize only ENQUEUE work and return without any
+ * host synchronisation: their rt_stats carry the host-known fields only (samples, launches), the
+ * output buffers of rt_finalize must be pinned host memory to stay asynchronous, and both the
+ * outputs and the timings / ray counts (rt_frame_stats) are valid once the caller has
+ * synchronised the stream.  With the frame's own stream every call returns with its work done. */
 int rt_frame_set_stream(rt_frame *, void *cuda_stream);
+/* Timings (CUDA events) and device counters of the last rt_render / rt_finalize on this frame.
+ * Call after the frame's stream has been synchronised (it synchronises on the recorded events). */
+int rt_frame_stats(rt_frame *, rt_stats *);
 
 /* --- the hot path: replaces the pixel/sample loops + ray_color + everything below
  *     (src/cpu/main.cc:12-30,111-123; GPU twin: render kernel, src/gpu/camera.h:169-195).
@@ -132,16 +154,31 @@ int rt_frame_reduce_local(rt_frame *, const rt_config *);
 int rt_finalize(rt_frame *, const rt_config *, const void *const *partials, uint32_t count,
                 uint8_t *rgb8_out, float *linear_out, rt_stats *);
 
-/* Convenience: render all slices on one GPU + reduce + finalise (host buffers out). */
+/* Convenience: render all slices on one GPU + reduce + finalise (host buffers out).  The frame
+ * object (0.83 GB of slice planes at 1200x675) is cached per calling thread and re-used by the
+ * next call with the same size and device; rt_release_cached_frames() frees the calling thread's. */
 int rt_render_image(const rt_scene *, const rt_camera *, const rt_config *, uint8_t *rgb8_out,
                     float *linear_out, rt_stats *);
+int rt_release_cached_frames(void);
 
-/* Same, with the frame's samples split over `ngpu` devices of this process (ngpu in {1,2,4,8}):
- * one host thread per GPU renders its block of canonical slices, the per-GPU partial sums are
- * copied to devices[0] over NVLink peer copies (no arithmetic in flight) and finalised there.
- * The image is byte-identical for every ngpu.  (Multi-process deployments use rt_render +
- * rt_frame_partial_ptr + rt_finalize with their own transport instead, see INTEGRATION.md.)
- * The reference has no multi-device path. */
+/* --- one process, several GPUs (ngpu in {1,2,4,8}); the reference has no multi-device path
+ *     (SURVEY.md §8e).  rt_multi owns one scene and one frame per device, set up once; a frame's
+ *     samples are split by canonical slices (device g renders slices [64g/G, 64(g+1)/G)), each GPU
+ *     pre-sums its sub-tree, and the finalise kernel on devices[0] reads the other GPUs' partial
+ *     buffers in place through NVLink peer pointers (no staging buffer, no copy; without peer
+ *     access they are copied to devices[0] first).  Everything is enqueued from the calling thread
+ *     and the call returns after ONE host synchronisation.  The image is byte-identical for every
+ *     ngpu.  (Multi-process deployments use rt_render + rt_frame_partial_ptr + rt_finalize with
+ *     their own transport instead, see INTEGRATION.md.) */
+typedef struct rt_multi rt_multi;
+int rt_multi_create(const int32_t *devices, uint32_t ngpu, uint32_t width, uint32_t height, rt_multi **out);
+/* Upload the scene to every device (first call allocates; later calls with a sphere count that
+ * fits re-use the allocations: one asynchronous copy per device, ordered before the next render). */
+int rt_multi_set_scene(rt_multi *, const rt_sphere *spheres, uint32_t n);
+int rt_multi_render(rt_multi *, const rt_camera *, const rt_config *, uint8_t *rgb8_out,
+                    float *linear_out, rt_stats *);
+int rt_multi_destroy(rt_multi *);
+/* Convenience: rt_multi_create + set_scene + render + destroy around one frame. */
 int rt_render_image_multi(const rt_sphere *spheres, uint32_t n, const rt_camera *, const rt_config *,
                           const int32_t *devices, uint32_t ngpu, uint8_t *rgb8_out,
                           float *linear_out, rt_stats *);
@@ -159,9 +196,24 @@ int rt_primary_hits(const rt_scene *, const rt_camera *, uint32_t width, uint32_
  *     measured with a register-resident micro-kernel; the roofline denominator of bench.py. */
 int rt_measure_fp32_peak(int32_t device, float *tflops, float *sm_clock_mhz_est);
 
-/* --- output: P3 text, rows top->bottom, "r g b\n" per pixel (src/cpu/main.cc:109,
- *     color.h:20-22). */
-int rt_write_ppm(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height);
+/* --- output stage (the step after the path): "P3\nW H\n255\n" + "r g b\n" per pixel, rows
+ *     top->bottom (src/cpu/main.cc:109, color.h:20-22; the multi-threaded program's loop,
+ *     src/cpu-multi-threading/main.cc:148-154), or binary P6.  path "-" = stdout. */
+#define RT_PNM_P3 3 /* text, the reference's format */
+#define RT_PNM_P6 6 /* binary */
+int rt_write_ppm(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height); /* P3 */
+int rt_write_pnm(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height, int format);
+/* Finalise in bands of rows: the finalise kernel runs once, then the 8-bit rows cross to the host
+ * through two pinned buffers and `fn` consumes band k (rows [row_begin, row_end), top->bottom,
+ * tightly packed RGB8) while the copy of band k+1 is in flight.  fn returns 0 to continue.
+ * Synchronous on every stream.  band_rows = 0 picks 64. */
+typedef int (*rt_band_fn)(void *user, const uint8_t *rgb8_rows, uint32_t row_begin, uint32_t row_end);
+int rt_finalize_bands(rt_frame *, const rt_config *, const void *const *partials, uint32_t count,
+                      uint32_t band_rows, rt_band_fn fn, void *user, rt_stats *);
+/* rt_finalize_bands with a PNM writer as the consumer: text formatting / fwrite of band k overlaps
+ * the device->host copy of band k+1; no whole-image host buffer. */
+int rt_finalize_to_file(rt_frame *, const rt_config *, const void *const *partials, uint32_t count,
+                        const char *path, int format, rt_stats *);
 
 #ifdef __cplusplus
 }

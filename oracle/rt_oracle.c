@@ -315,16 +315,24 @@ int orc_closest_hit(const double *spheres, int n, const double org[3], const dou
 
 void orc_primary_hits(const double *spheres, int n, const orc_camera *cam, int W, int H,
                       int32_t *ids, double *t, double *normal, uint8_t *front_face) {
+  orc_primary_hits_rows(spheres, n, cam, W, H, 0, H, ids, t, normal, front_face);
+}
+
+/* The same table for image rows [row_begin, row_end) only (outputs hold just those rows), so that
+ * full-size tables can be computed by several threads at test time. */
+void orc_primary_hits_rows(const double *spheres, int n, const orc_camera *cam, int W, int H,
+                           int row_begin, int row_end, int32_t *ids, double *t, double *normal,
+                           uint8_t *front_face) {
   v3 origin = ld3(cam->origin), llc = ld3(cam->lower_left);
   v3 hor = ld3(cam->horizontal), ver = ld3(cam->vertical), zero = V(0, 0, 0);
-  for (int row = 0; row < H; ++row) {
+  for (int row = row_begin; row < row_end; ++row) {
     int j = H - 1 - row;
     for (int i = 0; i < W; ++i) {
       double u = (i + 0.5) / (W - 1), v = (j + 0.5) / (H - 1); /* main.cc:116-117, xi=.5 */
       v3 org = vadd(origin, zero);
       v3 dir = vsub(vsub(vadd(vadd(llc, vscale(u, hor)), vscale(v, ver)), origin), zero);
       hitrec rec;
-      size_t px = (size_t)row * W + i;
+      size_t px = (size_t)(row - row_begin) * W + i;
       if (world_hit(spheres, n, org, dir, 0.001, INFINITY, &rec)) {
         ids[px] = rec.id; t[px] = rec.t; front_face[px] = (uint8_t)rec.front_face;
         st3(normal + px * 3, rec.normal);

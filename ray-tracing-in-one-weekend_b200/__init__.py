@@ -23,6 +23,8 @@ FLAG_COUNT_RAYS = 1
 FLAG_WAVEFRONT, FLAG_BVH = 4, 8
 FLAG_V4_MODEL = 16  # src/gpu (v4 book) semantics, see include/rt_b200.h
 FLAG_F32_HIT = 32   # f32 sphere::hit like src/gpu/sphere.h (compatibility/diagnostic)
+FLAG_NO_FILTER = 64  # soundness switch: no f32 pre-test, every ray resolves every sphere in f64
+PNM_P3, PNM_P6 = 3, 6
 
 
 class RtError(RuntimeError):
@@ -59,7 +61,12 @@ SYMBOLS = [
     "rt_scene_count", "rt_frame_create", "rt_frame_destroy", "rt_frame_partial_ptr", "rt_render",
     "rt_frame_reduce_local", "rt_finalize", "rt_render_image", "rt_primary_hits", "rt_write_ppm",
     "rt_frame_set_stream", "rt_measure_fp32_peak", "rt_render_image_multi",
+    "rt_scene_update", "rt_frame_stats", "rt_release_cached_frames", "rt_write_pnm",
+    "rt_finalize_bands", "rt_finalize_to_file", "rt_multi_create", "rt_multi_set_scene",
+    "rt_multi_render", "rt_multi_destroy",
 ]
+
+BAND_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint8), C.c_uint32, C.c_uint32)
 
 _lib = None
 
@@ -159,6 +166,23 @@ class Scene:
         self._h = C.c_void_p()
         _check(lib().rt_scene_create(arr, C.c_uint32(n), C.c_int32(device), C.byref(self._h)))
 
+    def update(self, rows: np.ndarray, cuda_stream: int | None = None) -> None:
+        """hittable_list::clear + add without re-allocating (rt_scene_update): one asynchronous
+        host->device copy from the scene's pinned staging buffer on `cuda_stream`."""
+        arr, n = spheres_from_rows(rows)
+        _check(lib().rt_scene_update(self._h, arr, C.c_uint32(n), C.c_void_p(cuda_stream or 0)))
+        self.n = n
+
+    def update_raw(self, arr, n: int, cuda_stream: int | None = None) -> None:
+        """rt_scene_update from a prepared ctypes rt_sphere array (no Python-side conversion)."""
+        _check(lib().rt_scene_update(self._h, arr, C.c_uint32(n), C.c_void_p(cuda_stream or 0)))
+        self.n = n
+
+    def blob_bytes(self) -> int:
+        """bytes one upload of this scene moves host->device (the four SoA row arrays)"""
+        cap = max((self.n + 7) // 8 * 8, 8)
+        return cap * 32 + (cap + 8) * 16 + cap * 16 + cap * 8
+
     def close(self):
         if self._h:
             lib().rt_scene_destroy(self._h)
@@ -196,6 +220,40 @@ class Frame:
     def reduce_local(self, cfg: Config) -> None:
         cf = cfg.c()
         _check(lib().rt_frame_reduce_local(self._h, C.byref(cf)))
+
+    def stats(self) -> Stats:
+        """Timings / ray count of the last render + finalise (after the stream was synchronised)."""
+        st = _Stats()
+        _check(lib().rt_frame_stats(self._h, C.byref(st)))
+        return Stats.of(st)
+
+    def finalize_to_file(self, cfg: Config, path: str, fmt: int = PNM_P3, partial_ptrs=None) -> Stats:
+        """Finalise straight into a PNM file, band by band (rt_finalize_to_file)."""
+        if partial_ptrs is None:
+            partial_ptrs = [self.partial_ptr()[0]]
+        n = len(partial_ptrs)
+        ptrs = (C.c_void_p * n)(*partial_ptrs)
+        st, cf = _Stats(), cfg.c()
+        _check(lib().rt_finalize_to_file(self._h, C.byref(cf), ptrs, C.c_uint32(n), path.encode(),
+                                         C.c_int(fmt), C.byref(st)))
+        return Stats.of(st)
+
+    def finalize_bands(self, cfg: Config, band_rows: int, fn, partial_ptrs=None) -> Stats:
+        """fn(rows uint8 [r1-r0][W][3], r0, r1) is called per band of rows, top to bottom."""
+        if partial_ptrs is None:
+            partial_ptrs = [self.partial_ptr()[0]]
+        n = len(partial_ptrs)
+        ptrs = (C.c_void_p * n)(*partial_ptrs)
+        W = self.width
+
+        def tramp(_user, p, r0, r1):
+            fn(np.ctypeslib.as_array(p, shape=(r1 - r0, W, 3)).copy(), r0, r1)
+            return 0
+        cb = BAND_FN(tramp)
+        st, cf = _Stats(), cfg.c()
+        _check(lib().rt_finalize_bands(self._h, C.byref(cf), ptrs, C.c_uint32(n), C.c_uint32(band_rows),
+                                       cb, None, C.byref(st)))
+        return Stats.of(st)
 
     def finalize(self, cfg: Config, partial_ptrs=None, want_linear=False, rgb_out=None,
                  linear_out=None):
@@ -252,6 +310,45 @@ def render_image_multi(rows: np.ndarray, cam: Camera, cfg: Config, devices, want
     return rgb, lin, Stats.of(st)
 
 
+class Multi:
+    """One process, several GPUs (rt_multi_*): scenes, frames and peer access set up once."""
+
+    def __init__(self, devices, width: int, height: int):
+        self.devices, self.width, self.height = list(devices), width, height
+        self._h = C.c_void_p()
+        devs = (C.c_int32 * len(self.devices))(*self.devices)
+        _check(lib().rt_multi_create(devs, C.c_uint32(len(self.devices)), C.c_uint32(width),
+                                     C.c_uint32(height), C.byref(self._h)))
+
+    def set_scene(self, rows: np.ndarray) -> None:
+        arr, n = spheres_from_rows(rows)
+        _check(lib().rt_multi_set_scene(self._h, arr, C.c_uint32(n)))
+
+    def render(self, cam: Camera, cfg: Config, want_linear=False, rgb_out=None):
+        rgb = rgb_out if rgb_out is not None else np.empty((self.height, self.width, 3), np.uint8)
+        lin = np.empty((self.height, self.width, 3), np.float32) if want_linear else None
+        st, cc, cf = _Stats(), cam.c(), cfg.c()
+        _check(lib().rt_multi_render(self._h, C.byref(cc), C.byref(cf), C.c_void_p(rgb.ctypes.data),
+                                     C.c_void_p(lin.ctypes.data) if lin is not None else None,
+                                     C.byref(st)))
+        return rgb, lin, Stats.of(st)
+
+    def close(self):
+        if self._h:
+            lib().rt_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def release_cached_frames() -> None:
+    _check(lib().rt_release_cached_frames())
+
+
 def primary_hits(scene: Scene, cam: Camera, width: int, height: int, use_f64: bool, device=0):
     """-> ids int32 [H][W], t f64 [H][W], normal f64 [H][W][3], front_face u8 [H][W]"""
     ids = np.empty((height, width), np.int32)
@@ -273,8 +370,8 @@ def measure_fp32_peak(device: int = 0):
     return tf.value, mhz.value
 
 
-def write_ppm(path: str, rgb8: np.ndarray) -> None:
+def write_ppm(path: str, rgb8: np.ndarray, fmt: int = PNM_P3) -> None:
     h, w, _ = rgb8.shape
     rgb8 = np.ascontiguousarray(rgb8, np.uint8)
-    _check(lib().rt_write_ppm(path.encode(), C.c_void_p(rgb8.ctypes.data), C.c_uint32(w),
-                              C.c_uint32(h)))
+    _check(lib().rt_write_pnm(path.encode(), C.c_void_p(rgb8.ctypes.data), C.c_uint32(w),
+                              C.c_uint32(h), C.c_int(fmt)))

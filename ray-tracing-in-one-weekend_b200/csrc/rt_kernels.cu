@@ -5,15 +5,11 @@
 //   finalize_kernel   upper tree levels over per-GPU partials + write_color (color.h:8-23).
 //   primary_f32       production-precision primary-hit table (accuracy gate, f32 leg).
 //
-// Design notes (full text in DESIGN.md):
-//  * Work item = (pixel, sample slice); a lane owns R items at a time and sums its samples
-//    sequentially in f32, so the image is independent of scheduling and of the GPU count.
-//  * The sphere loop is a conservative f32 LINE-sphere filter, 7 FFMA + 1 FSETP per
-//    (ray, sphere), on SoA float4 rows staged in shared memory by a 1-D bulk (TMA) copy.
-//    Survivors (a handful per ray) are pushed to a per-lane candidate list and resolved in
-//    f64 with exactly the reference's sphere::hit arithmetic, so closest-hit decisions do
-//    not suffer f32 cancellation (r = 1000 ground sphere).
-#include <cstdlib>
+//   cost order        hand-out order of the next frame's work queue (pixels by ray count).
+//   ffma_peak         FP32 FFMA throughput micro-kernel (roofline denominator of bench.py).
+//
+// All of these stream once over per-pixel buffers (HBM-bound, 16 B per pixel and input plane);
+// together they are < 0.1 % of a frame.  Design notes: DESIGN.md section 4.2.
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
@@ -240,7 +236,7 @@ cudaError_t launch_cost_order(const float4 *partial, uint32_t npix, float inv_sa
   // pixels whose paths are long on average (glass, facing mirrors) are where the rare 50-bounce
   // paths live: ALL their slices are handed out before anything else
   unsigned quarter_rays = 4u * kHeavyRays;
-  if (const char *e = getenv("RT_B200_HEAVY_QUARTER_RAYS")) quarter_rays = (unsigned)atoi(e);  // tuning knob
+  if (env_cfg().heavy_quarter_rays >= 0) quarter_rays = (unsigned)env_cfg().heavy_quarter_rays;  // tuning knob
   if (quarter_rays > 255u) quarter_rays = 255u;
   cost_keys_kernel<<<grid, 256, 0, st>>>(partial, npix, inv_samples, quarter_rays, heavy_only, keys, iota);
   cudaError_t e = cudaGetLastError();

@@ -46,6 +46,7 @@ struct WaveParams {
   uint32_t slice_begin, slice_end;
   uint32_t n_orders;            // slices handed out (hand-out order, trailing empty slices trimmed)
   uint32_t model_v4;            // 1 = src/gpu semantics (RT_FLAG_V4_MODEL): strict root interval, fuzz on the sphere
+  uint32_t no_filter;           // 1 = RT_FLAG_NO_FILTER: no f32 pre-test, every ray resolves every sphere in f64
   float4 *accum;                // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
   unsigned long long *counter;  // work-queue head (zeroed before the frame)
   unsigned int *live;           // rays produced by the last polled shade pass
@@ -61,6 +62,17 @@ struct WaveParams {
   uint32_t *cand_cnt;  // candidate entries per ray (> kCandPlanes = overflow)
   uint32_t *cand_idx;  // [kCandPlanes][n_slots] {group << kCandShift | row mask}, ascending
 };
+
+// RT_B200_* experiment switches, read ONCE per process.
+struct EnvCfg {
+  int mode;                 // RT_B200_MODE: -1 unset, 0 fused, 2 two-kernel wavefront
+  bool no_const_rows;       // RT_B200_NO_CONST_ROWS
+  bool no_cost_order;       // RT_B200_NO_COST_ORDER
+  int rays_per_lane;        // RT_B200_RAYS_PER_LANE (2 or 4)
+  int heavy_quarter_rays;   // RT_B200_HEAVY_QUARTER_RAYS, -1 unset
+  long wave_slots;          // RT_B200_WAVE_SLOTS, 0 unset
+};
+const EnvCfg &env_cfg();
 
 struct WaveRunInfo {
   uint32_t launches, waves, n_slots;

@@ -22,7 +22,6 @@
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
-#include <cstdlib>
 #include <cstring>
 
 namespace rtb {
@@ -305,7 +304,8 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
           const float4 S = __ldg(fast + s);
           const float b = fmaf(S.x, RD.x, fmaf(S.y, RD.y, fmaf(S.z, RD.z, nod)));
           const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
-          if (e >= oot && s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
+          // RT_FLAG_NO_FILTER: no pre-test at all -- hittable_list::hit as written (hittable_list.h:28-43)
+          if ((e >= oot || P.no_filter) && s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
         }
       }
     }
@@ -705,7 +705,11 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
     if (__all_sync(0xffffffffu, live == 0u)) break;  // warp-uniform exit keeps the loop convergent
 #endif
     if (BVH) bvh_trace<R>(P, exact, base, stride);
-    else filter_rays<R, G, CROWS>(P, CR, base, stride);
+    else if (P.no_filter) {
+      // soundness switch: no candidates are recorded, every slot takes the full-scan branch
+#pragma unroll
+      for (int r = 0; r < R; ++r) P.cand_cnt[base + r * stride] = kCandPlanes + 1u;
+    } else filter_rays<R, G, CROWS>(P, CR, base, stride);
   }
 }
 
@@ -760,10 +764,9 @@ cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_c
                           WaveRunInfo *info) {
   static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
   const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
-                     !getenv("RT_B200_NO_CONST_ROWS");
+                     !env_cfg().no_const_rows;
   if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
-  int rpl = 2;
-  if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
+  const int rpl = env_cfg().rays_per_lane;
   if (rpl != 2 && rpl != 4) return cudaErrorInvalidValue;
   if (p.n_slots % (kWBlock * 4u)) return cudaErrorInvalidValue;
 
@@ -873,10 +876,9 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
   if (use_bvh && f32_hit) return cudaErrorInvalidValue;
   static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
   const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
-                     !getenv("RT_B200_NO_CONST_ROWS");
+                     !env_cfg().no_const_rows;
   if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
-  int rpl = 2;
-  if (const char *e = getenv("RT_B200_RAYS_PER_LANE")) rpl = atoi(e);
+  const int rpl = env_cfg().rays_per_lane;
   if (rpl != 2 && rpl != 4) return cudaErrorInvalidValue;
   const size_t scene_smem = (size_t)p.scene.n_pad * 56;
   const bool in_smem = (scene_smem + 1024) * RTW_MINB <= smem_optin_max;

@@ -36,6 +36,29 @@ def test_multi_gpu_image_is_byte_identical(rt, name):
         assert np.array_equal(lin, base_lin), f"G={G}: linear sums differ"
 
 
+def test_persistent_multi_object_is_byte_identical(rt):
+    """rt_multi_*: scenes, frames and peer access set up once; device 0's finalise kernel reads the
+    other GPUs' partials through peer pointers.  Several frames (different seeds, then another
+    scene) through the same object equal the single-GPU images byte for byte."""
+    ndev = device_count(rt)
+    if ndev < 2:
+        pytest.skip("needs at least two GPUs")
+    W, H, spp = 160, 90, 64
+    for G in (2, 4, 8):
+        if G > ndev:
+            break
+        m = rt.Multi(list(range(G)), W, H)
+        for name, seed in (("cover", 1), ("cover", 2), ("three", 3)):
+            rows = golden(f"{name}_small.npz")["spheres"]
+            cam, cfg = cam_for(rt, name, W, H), rt.Config(W, H, spp, 50, seed=seed)
+            m.set_scene(rows)
+            rgb, lin, st = m.render(cam, cfg, want_linear=True)
+            base_rgb, base_lin, base_st = rt.render_image(rt.Scene(rows), cam, cfg)
+            assert st.rays == base_st.rays and st.samples == base_st.samples
+            assert np.array_equal(rgb, base_rgb) and np.array_equal(lin, base_lin), f"G={G} {name}"
+        m.close()
+
+
 def test_multi_gpu_argument_errors(rt):
     rows = golden("three_small.npz")["spheres"]
     cam = cam_for(rt, "three", 32, 18)
