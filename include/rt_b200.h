@@ -66,7 +66,6 @@ typedef struct rt_config {
 } rt_config;
 
 #define RT_FLAG_COUNT_RAYS 1u /* fill rt_stats.rays (one atomic per work item) */
-#define RT_FLAG_WAVEFRONT 4u  /* two-kernel shade/filter wavefront instead of the fused persistent kernel */
 #define RT_FLAG_BVH 8u        /* closest hit through the host-built BVH instead of the brute-force scan
                                  over the reference's sphere order (same hit, same image) */
 #define RT_FLAG_V4_MODEL 16u  /* the semantics of the reference's CUDA program (src/gpu/, v4 book) instead
@@ -79,13 +78,13 @@ typedef struct rt_config {
                                  sphere::hit arithmetic of src/gpu/sphere.h:15-47 (un-normalised direction,
                                  f32 hit point, no self-skip) instead of f64.  Reproduces the cancellation of
                                  |oc|^2 - r^2 on the r = 1000 ground sphere that darkens the reference CUDA
-                                 program's ground; brute-force fused mode only (not with RT_FLAG_BVH /
-                                 RT_FLAG_WAVEFRONT). */
+                                 program's ground; brute-force scan only (not with RT_FLAG_BVH). */
 #define RT_FLAG_NO_FILTER 64u /* debug/soundness switch: the f32 line-sphere pre-test of the brute-force scan is
                                  switched off and every ray resolves EVERY sphere in f64 (hittable_list::hit as
                                  written, src/cpu/hittable_list.h:28-43).  The image must be byte-identical with
                                  and without it: that is the test of the filter's conservativeness
-                                 (tests/test_filter_soundness.py).  ~50x slower; brute-force fused mode only. */
+                                 (tests/test_filter_soundness.py).  ~50x slower; brute-force scan only. */
+#define RT_FLAG_ALL (RT_FLAG_COUNT_RAYS | RT_FLAG_BVH | RT_FLAG_V4_MODEL | RT_FLAG_F32_HIT | RT_FLAG_NO_FILTER)
 
 typedef struct rt_stats {
   uint64_t samples;      /* samples traced by this call */

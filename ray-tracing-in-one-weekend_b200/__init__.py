@@ -20,7 +20,7 @@ LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
 SLICES = 64
 FLAG_COUNT_RAYS = 1
-FLAG_WAVEFRONT, FLAG_BVH = 4, 8
+FLAG_BVH = 8
 FLAG_V4_MODEL = 16  # src/gpu (v4 book) semantics, see include/rt_b200.h
 FLAG_F32_HIT = 32   # f32 sphere::hit like src/gpu/sphere.h (compatibility/diagnostic)
 FLAG_NO_FILTER = 64  # soundness switch: no f32 pre-test, every ray resolves every sphere in f64

@@ -41,16 +41,11 @@ namespace rtb {
 const EnvCfg &env_cfg() {
   static const EnvCfg cfg = [] {
     EnvCfg c;
-    const char *e = getenv("RT_B200_MODE");
-    c.mode = e ? (strcmp(e, "wave") == 0 ? 2 : 0) : -1;
+    const char *e;
     c.no_const_rows = getenv("RT_B200_NO_CONST_ROWS") != nullptr;
     c.no_cost_order = getenv("RT_B200_NO_COST_ORDER") != nullptr;
-    e = getenv("RT_B200_RAYS_PER_LANE");
-    c.rays_per_lane = e ? atoi(e) : 2;
     e = getenv("RT_B200_HEAVY_QUARTER_RAYS");
     c.heavy_quarter_rays = e ? atoi(e) : -1;
-    e = getenv("RT_B200_WAVE_SLOTS");
-    c.wave_slots = e ? atol(e) : 0;
     return c;
   }();
   return cfg;
@@ -283,8 +278,10 @@ CameraF32 rt_narrow_camera(const CamFrame &f, uint32_t W, uint32_t H, bool pixel
 extern "C" int rt_frame_create(uint32_t width, uint32_t height, int32_t device, rt_frame **out) {
   if (!out) return fail(RT_E_INVALID, "out is NULL");
   *out = nullptr;
-  if (width < 2 || height < 2 || (uint64_t)width * height >= (1ull << kItemShift))
-    return fail(RT_E_INVALID, "image size %ux%u out of range (min 2x2)", width, height);
+  if (width < 2 || height < 2 || width > 65535u || height > 65535u ||
+      (uint64_t)width * height >= (1ull << kItemShift))
+    return fail(RT_E_INVALID, "image size %ux%u out of range (2..65535 per side, fewer than 2^%u pixels)",
+                width, height, kItemShift);
   CU(cudaSetDevice(device));
   rt_frame *f = new (std::nothrow) rt_frame();
   if (!f) return fail(RT_E_NOMEM, "out of host memory");
@@ -318,7 +315,7 @@ extern "C" int rt_frame_destroy(rt_frame *f) {
   cudaSetDevice(f->device);
   cudaFree(f->accum); cudaFree(f->partial); cudaFree(f->rgb_words); cudaFree(f->linear);
   cudaFree(f->counters);
-  cudaFree(f->pool); cudaFree(f->live);
+  cudaFree(f->pool);
   cudaFree(f->order); cudaFree(f->sort_keys); cudaFree(f->sort_keys_out); cudaFree(f->sort_iota);
   cudaFree(f->sort_temp); cudaFree(f->heavy);
   if (f->host_words) cudaFreeHost(f->host_words);
@@ -354,12 +351,11 @@ static int check_cfg(const rt_config *cfg, const rt_frame *f) {
     return fail(RT_E_INVALID, "slices [%u,%u) must be an aligned power-of-two block of %u",
                 cfg->slice_begin, cfg->slice_end, RT_SLICES);
   if (cfg->samples_per_pixel == 0) return fail(RT_E_INVALID, "samples_per_pixel must be > 0");
-  if ((cfg->flags & RT_FLAG_F32_HIT) && (cfg->flags & (RT_FLAG_BVH | RT_FLAG_WAVEFRONT)))
-    return fail(RT_E_INVALID, "RT_FLAG_F32_HIT works with the brute-force fused kernel only");
-  if ((cfg->flags & RT_FLAG_NO_FILTER) && (cfg->flags & (RT_FLAG_BVH | RT_FLAG_WAVEFRONT | RT_FLAG_F32_HIT)))
-    return fail(RT_E_INVALID, "RT_FLAG_NO_FILTER works with the brute-force fused kernel only");
-  if ((cfg->flags & RT_FLAG_BVH) && (cfg->flags & RT_FLAG_WAVEFRONT))
-    return fail(RT_E_INVALID, "RT_FLAG_BVH is not available in the two-kernel wavefront form");
+  if ((cfg->flags & RT_FLAG_F32_HIT) && (cfg->flags & RT_FLAG_BVH))
+    return fail(RT_E_INVALID, "RT_FLAG_F32_HIT works with the brute-force scan only");
+  if ((cfg->flags & RT_FLAG_NO_FILTER) && (cfg->flags & (RT_FLAG_BVH | RT_FLAG_F32_HIT)))
+    return fail(RT_E_INVALID, "RT_FLAG_NO_FILTER works with the brute-force scan only");
+  if (cfg->flags & ~RT_FLAG_ALL) return fail(RT_E_INVALID, "unknown flag bits 0x%x", cfg->flags & ~RT_FLAG_ALL);
   return RT_OK;
 }
 
@@ -374,30 +370,16 @@ static uint64_t samples_of(const rt_config *cfg, uint32_t npix) {
 }
 
 // ---------------------------------------------------------------- the hot path
-// 0 = fused persistent kernel (default), 2 = two-kernel wavefront (A/B variant of the same code)
-static int render_mode(const rt_config *cfg) {
-  if (cfg->flags & (RT_FLAG_F32_HIT | RT_FLAG_BVH | RT_FLAG_NO_FILTER)) return 0;
-  if (env_cfg().mode >= 0) return env_cfg().mode;
-  return (cfg->flags & RT_FLAG_WAVEFRONT) ? 2 : 0;
-}
-
-// path-slot pool + live counter, allocated on first use; committed to the frame only when every
-// allocation succeeded
+// path-slot pool, allocated on first use
 static int ensure_pool(rt_frame *f) {
   if (f->pool) return RT_OK;
-  uint32_t slots = wave_default_slots(f->sm_count);
-  if (env_cfg().wave_slots) slots = (uint32_t)env_cfg().wave_slots / 1024u * 1024u;
-  if (slots < 1024u) return fail(RT_E_INVALID, "RT_B200_WAVE_SLOTS too small");
-  void *pool = nullptr;
-  unsigned int *live = nullptr;
-  CU(cudaMalloc(&pool, wave_pool_bytes(slots)));
-  CU_OR(cudaFree(pool), cudaMalloc(&live, sizeof(unsigned int)));
-  f->pool = pool; f->live = live; f->pool_slots = slots;
+  const uint32_t slots = wave_default_slots(f->sm_count);
+  CU(cudaMalloc(&f->pool, wave_pool_bytes(slots)));
+  f->pool_slots = slots;
   return RT_OK;
 }
 
-// Enqueue the path kernel(s) of one frame's slices on the frame's stream (no host sync in the
-// fused form; the two-kernel wavefront polls a live counter and therefore synchronises).
+// Enqueue the path kernel of one frame's slices on the frame's stream (no host synchronisation).
 int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config *cfg, rt_frame *f) {
   if (!sc || !cam) return fail(RT_E_INVALID, "NULL argument");
   int rc = check_cfg(cfg, f);
@@ -415,9 +397,9 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
   w.no_filter = (cfg->flags & RT_FLAG_NO_FILTER) ? 1u : 0u;
   w.cam = rt_narrow_camera(cf, f->w, f->h, w.model_v4 != 0u);
   w.width = f->w; w.height = f->h;
+  w.inv_width = 1.0f / (float)f->w;
   w.spp = cfg->samples_per_pixel; w.max_depth = cfg->max_depth;
   w.seed = cfg->seed; w.sample_offset = cfg->sample_offset;
-  w.slice_begin = cfg->slice_begin; w.slice_end = cfg->slice_end;
   w.accum = f->accum; w.counter = f->counters;
   w.order = f->order_valid && f->order_heavy_only == use_bvh && !env_cfg().no_cost_order ? f->order : nullptr;
   w.heavy = f->heavy;
@@ -426,10 +408,20 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
   // hand-out order = largest slices first; trailing slices without samples are not queued
   const uint32_t n_own = cfg->slice_end - cfg->slice_begin;
   w.n_orders = 0;
+  memset(w.order_slice, 0, sizeof w.order_slice);
   for (uint32_t ord = 0; ord < n_own; ++ord) {
     uint32_t a, b;
-    slice_range(slice_in_order(ord, cfg->slice_begin, cfg->slice_end), cfg->samples_per_pixel, a, b);
+    const uint32_t sl = slice_in_order(ord, cfg->slice_begin, cfg->slice_end);
+    w.order_slice[ord] = (uint8_t)sl;
+    slice_range(sl, cfg->samples_per_pixel, a, b);
     if (b > a) w.n_orders = ord + 1;
+  }
+  // canonical slices are contiguous sample ranges: slice s = [bounds[s], bounds[s + 1])
+  for (uint32_t sl = 0; sl < RT_SLICES; ++sl) {
+    uint32_t a, b;
+    slice_range(sl, cfg->samples_per_pixel, a, b);
+    w.slice_bounds[sl] = a;
+    w.slice_bounds[sl + 1] = b;
   }
 
   uint32_t launches = 0;
@@ -445,16 +437,9 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
       CU(cudaMemsetAsync(f->accum + (size_t)slice_in_order(ord, cfg->slice_begin, cfg->slice_end) * f->npix,
                          0, (size_t)f->npix * sizeof(float4), f->stream));
     if ((rc = ensure_pool(f)) != RT_OK) return rc;
-    w.live = f->live;
     WaveRunInfo info;
-    if (render_mode(cfg) == 2) {
-      wave_carve(w, f->pool, f->pool_slots);
-      CU(run_wavefront(w, sc->host_fast.data(), f->sm_count, f->smem_optin, f->stream,
-                       reinterpret_cast<unsigned int *>(f->host_words + 2), &info));
-    } else {
-      CU(run_fused(w, f->pool, f->pool_slots, sc->host_fast.data(), use_bvh,
-                   (cfg->flags & RT_FLAG_F32_HIT) != 0, f->sm_count, f->smem_optin, f->stream, &info));
-    }
+    CU(run_fused(w, f->pool, f->pool_slots, sc->host_fast.data(), use_bvh,
+                 (cfg->flags & RT_FLAG_F32_HIT) != 0, f->sm_count, f->smem_optin, f->stream, &info));
     launches = info.launches;
   }
   CU(cudaEventRecord(f->ev[1], f->stream));

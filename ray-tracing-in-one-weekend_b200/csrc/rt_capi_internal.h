@@ -57,7 +57,7 @@ struct rt_frame {
   uint32_t *rgb_words;
   float *linear;
   unsigned long long *counters;    // device: [0] work queue head, [1] ray total
-  unsigned long long *host_words;  // pinned: [1] ray total of the last finalise, [2] wavefront live counter
+  unsigned long long *host_words;  // pinned: [1] ray total of the last finalise
   cudaStream_t stream;      // stream in use (own_stream unless rt_frame_set_stream)
   cudaStream_t own_stream;
   cudaEvent_t ev[4];        // render begin/end, finalise begin/end
@@ -69,7 +69,6 @@ struct rt_frame {
   bool rendered, finalized;
   void *pool;               // path-slot pool (allocated on first use)
   uint32_t pool_slots;
-  unsigned int *live;       // device counter of the two-kernel wavefront
   // hand-out order of the next frame: pixels by descending cost of the frame rendered before
   uint32_t *order, *sort_keys, *sort_keys_out, *sort_iota, *heavy;
   void *sort_temp;

@@ -46,6 +46,7 @@ struct CameraF64 {
 // Relative slack of the f32 line-sphere filter (see DESIGN.md "filter error bound").
 #define RTB_FILTER_SLACK 1.9073486328125e-06f /* 32 * 2^-24 */
 
+// @phase fetch
 // ---------------------------------------------------------------- canonical sample slices
 // The spp samples of a pixel are cut into 64 canonical slices in 8 blocks of 8.  Block b covers
 // [floor(b*spp/8), floor((b+1)*spp/8)); inside a block the slices take 13, 12, 10, 9, 8, 6, 3, 1
@@ -76,6 +77,7 @@ __host__ __device__ __forceinline__ uint32_t slice_in_order(uint32_t order_idx, 
   return sb + (order_idx % nb) * 8u + order_idx / nb;
 }
 
+// @phase philox
 // ---------------------------------------------------------------- Philox4x32-10
 // Stream contract (identical in oracle/rt_oracle.c):
 //   key = (pixel index in output order, absolute sample index)
@@ -103,6 +105,7 @@ __device__ __forceinline__ float4 philox_uniforms(uint32_t pixel, uint32_t sampl
                      (float)(o.w >> 8) * s);
 }
 
+// @phase scatter
 // ---------------------------------------------------------------- samplers
 // Direct, distribution-equivalent forms of the reference's rejection loops.
 __device__ __forceinline__ void unit_vector_from(float x0, float x1, float &ux, float &uy,
@@ -114,6 +117,7 @@ __device__ __forceinline__ void unit_vector_from(float x0, float x1, float &ux, 
   ux = rxy * c; uy = rxy * s; uz = z;
 }
 
+// @phase gate
 // ---------------------------------------------------------------- exact candidate test
 // sphere::hit (src/cpu/sphere.h:24-51) in double on the f32 ray; returns true and updates
 // t_best when the root lies in [t_min, t_best] (inclusive upper bound: a later sphere with
@@ -137,6 +141,7 @@ __device__ __forceinline__ bool exact_hit(const double4 S, double ox, double oy,
   return true;
 }
 
+// @phase stage
 // ---------------------------------------------------------------- bulk copy (TMA 1-D)
 __device__ __forceinline__ uint32_t smem_addr(const void *p) {
   return (uint32_t)__cvta_generic_to_shared(p);

@@ -29,71 +29,66 @@ struct ConstRows {
   float4 row[kConstRows];
 };
 
-// ---------------------------------------------------------------- wavefront form (rt_wave.cu)
-#ifndef RTW_CAND_PLANES
-#define RTW_CAND_PLANES 64
+// ---------------------------------------------------------------- path kernel (rt_wave.cu)
+// A warp owns 64 path slots for the whole frame (2 per lane).  Rays and the closest-hit records of
+// a wave live in the warp's shared memory; the rest of a slot's state (throughput, item sums, item)
+// lives in a pool in device memory (L2-resident).
+#ifndef RTW_LIST_SMEM
+#define RTW_LIST_SMEM 160
 #endif
-constexpr unsigned kCandPlanes = RTW_CAND_PLANES;  // candidate entries kept per ray before the full scan of shade_slot
-constexpr unsigned kCandShift = 8;    // entry = first row of a decision group << kCandShift | row mask
+constexpr unsigned kListSmem = RTW_LIST_SMEM;   // candidate entries of a warp and wave kept in shared memory
+constexpr unsigned kListGlobalPerSlot = 64;     // ... and this many more per slot in the pool (x 64 slots per warp)
+constexpr unsigned kGroupBits = 26;             // entry = local slot << kGroupBits | decision group (row / G)
 
 struct WaveParams {
   SceneView scene;
   CameraF32 cam;
   uint32_t width, height;
+  float inv_width;              // 1 / width (pixel -> row estimate, fixed up exactly)
   uint32_t spp, max_depth;
   uint64_t seed;
   uint32_t sample_offset;
-  uint32_t slice_begin, slice_end;
   uint32_t n_orders;            // slices handed out (hand-out order, trailing empty slices trimmed)
   uint32_t model_v4;            // 1 = src/gpu semantics (RT_FLAG_V4_MODEL): strict root interval, fuzz on the sphere
   uint32_t no_filter;           // 1 = RT_FLAG_NO_FILTER: no f32 pre-test, every ray resolves every sphere in f64
   float4 *accum;                // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
   unsigned long long *counter;  // work-queue head (zeroed before the frame)
-  unsigned int *live;           // rays produced by the last polled shade pass
   const uint32_t *order;        // pixel hand-out order within a slice (nullptr = scan order)
   const uint32_t *heavy;        // leading pixels of `order` whose slices are all handed out first
   // pool of path slots (SoA, n_slots each)
   uint32_t n_slots;
-  float4 *ray_o;       // {ox, oy, oz, |d| of the reference's un-normalised ray; < 0 = no ray}
-  float4 *ray_d;       // {unit direction, -}
   float4 *thr;         // {throughput r, g, b, depth (int bits): >0 bounces left, 0 new path, -1 retired}
   float4 *acc;         // {item sum r, g, b, ray segments}
   uint4 *it;           // {slice << kItemShift | pixel, next sample, slice end, -}
-  uint32_t *cand_cnt;  // candidate entries per ray (> kCandPlanes = overflow)
-  uint32_t *cand_idx;  // [kCandPlanes][n_slots] {group << kCandShift | row mask}, ascending
+  uint32_t *glist;     // [n_slots * kListGlobalPerSlot] candidate entries beyond a warp's shared-memory list
+  // per-lane indexed tables (constant bank): slice handed out at position k of the hand-out order,
+  // and the sample range [bounds[s], bounds[s + 1]) of canonical slice s
+  uint8_t order_slice[64];
+  uint32_t slice_bounds[65];
 };
 
 // RT_B200_* experiment switches, read ONCE per process.
 struct EnvCfg {
-  int mode;                 // RT_B200_MODE: -1 unset, 0 fused, 2 two-kernel wavefront
   bool no_const_rows;       // RT_B200_NO_CONST_ROWS
   bool no_cost_order;       // RT_B200_NO_COST_ORDER
-  int rays_per_lane;        // RT_B200_RAYS_PER_LANE (2 or 4)
   int heavy_quarter_rays;   // RT_B200_HEAVY_QUARTER_RAYS, -1 unset
-  long wave_slots;          // RT_B200_WAVE_SLOTS, 0 unset
 };
 const EnvCfg &env_cfg();
 
 struct WaveRunInfo {
-  uint32_t launches, waves, n_slots;
-  int rays_per_lane, filter_grid, shade_grid;
+  uint32_t launches, n_slots;
+  int rays_per_lane, grid;
   bool rows_in_constant_bank, scene_in_smem;
 };
 
 size_t wave_pool_bytes(uint32_t n_slots);
 uint32_t wave_default_slots(int sm_count);
-void wave_carve(WaveParams &p, void *pool, uint32_t n_slots);
-// Runs one frame's slices: init, then shade/filter waves until no ray is left.  Synchronises
-// the stream (it polls the live-ray counter through host_live, pinned host memory).
-cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_count,
-                          size_t smem_optin_max, cudaStream_t st, unsigned int *host_live,
-                          WaveRunInfo *info);
 
 // Host-side BVH build over {cx, cy, cz, signed r} (rt_bvh.cu).
 void build_bvh(const double4 *spheres, uint32_t n, std::vector<BvhNode> &nodes,
                std::vector<uint32_t> &prim);
 
-// Fused persistent form: one launch per frame; carves n_slots = grid * block * R out of the pool.
+// The persistent path kernel: one launch per frame; carves n_slots = grid * block * 2 out of the pool.
 // use_bvh: closest hit by BVH traversal (scene.bvh_nodes) instead of the brute-force filter.
 // f32_hit: candidate resolution in f32 like src/gpu/sphere.h (RT_FLAG_F32_HIT; brute force only).
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,

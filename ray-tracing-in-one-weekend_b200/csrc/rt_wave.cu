@@ -1,24 +1,27 @@
 // csrc/rt_wave.cu — the path-tracing hot path (sm_100a): everything executed per (pixel, sample)
 // of src/cpu/main.cc:111-123.
 //
-// Path state lives in a pool of slots in device memory (L2-resident); two device functions
-// alternate over it:
+// fused_kernel is a persistent kernel.  A WARP owns 64 path slots for the whole frame (two per
+// lane).  The rays of a wave and their closest-hit records live in the warp's shared memory; the
+// rest of a slot's state (throughput, item sums, item) in a pool in device memory (L2-resident).
+// Every wave runs three phases, the divergent ones compacted across the warp's 64 slots:
 //
-//   shade_slot     one slot.  Finishes the ray segment traced by the previous pass: f64 resolution
-//                  of the filter's candidates (sphere::hit, src/cpu/sphere.h:24-51), sky or material
-//                  scatter (main.cc:12-30, material.h), then, if the path ended, path regeneration:
-//                  next sample of the slot's (pixel, slice) item or the next item of the frame's
-//                  work queue, camera::get_ray (camera.h:28-35).
-//   filter_rays    R slots of one lane.  Conservative f32 line-sphere test of R rays against ALL
-//                  spheres in reference order (hittable_list::hit visits every object,
-//                  hittable_list.h:28-43): packed FFMA2, sphere rows through the constant bank
-//                  into uniform registers.  Survivors are recorded as {group, row mask} entries in
-//                  the slot's candidate planes.  The lane carries no path state, only rays.
-//   bvh_trace      optional replacement of filter_rays: closest hit through the host-built BVH.
-//
-// fused_kernel is the product: a persistent kernel in which every lane owns R slots for the whole
-// frame and alternates the two phases.  shade_kernel / filter_kernel run the same functions as a
-// two-kernel wavefront (A/B variant, RT_FLAG_WAVEFRONT).
+//   shade     one slot per lane and step (two steps).  Finishes the ray segment traced by the
+//             previous wave from its closest-hit record: sky or material scatter (main.cc:12-30,
+//             material.h), then, if the path ended, path regeneration: next sample of the slot's
+//             (pixel, slice) item or the next item of the frame's work queue (table-driven
+//             decode), camera::get_ray (camera.h:28-35).
+//   filter    two rays per lane.  Conservative f32 line-sphere test against ALL spheres in
+//             reference order (hittable_list::hit visits every object, hittable_list.h:28-43):
+//             packed FFMA2, sphere rows through the constant bank into uniform registers.  A
+//             decision group of 4 rows that some ray passes is recorded as ONE entry
+//             {slot, group} in the warp's candidate list, appended with ballots (no per-lane
+//             counters, no divergent code).
+//   resolve   the warp walks its candidate list 32 entries at a time, whatever slot they belong
+//             to: f32 re-test of the group's 4 rows, then sphere::hit in f64 (sphere.h:24-51) on
+//             the survivors, and the slot's closest-hit record is updated under the reference's
+//             tie rule.  Lanes are balanced by ENTRY, not by slot.
+//   bvh_trace optional replacement of filter + resolve: closest hit through the host-built BVH.
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
@@ -33,7 +36,21 @@ namespace rtb {
 #define RTW_MINB 3
 #endif
 constexpr int kWBlock = RTW_BLOCK;
+constexpr int kWarps = kWBlock / 32;
+constexpr unsigned FULL = 0xffffffffu;
+constexpr unsigned long long kInfKey = 0x7ff0000000000000ull;  // +inf as a double: no hit yet
+constexpr uint32_t kNoItem = 0xffffffffu;
 
+// Shared memory of one warp: the 64 rays of the wave, their closest-hit records, the candidate list.
+struct __align__(16) WarpState {
+  float4 ro[64];               // {ox, oy, oz, |d| of the reference's un-normalised ray; < 0 = no ray}
+  float4 rd[64];               // {unit direction, index of the sphere the ray just left (int bits) or -1}
+  unsigned long long key[64];  // root numerator of the closest hit so far (bits of a positive double)
+  int id[64];                  // its sphere, -1 = none
+  uint32_t list[kListSmem];    // {slot << kGroupBits | decision group}, ascending groups
+};
+
+// @phase helpers
 __device__ __forceinline__ float2 wffma2(float2 a, float2 b, float2 c) {
   unsigned long long ra = *reinterpret_cast<unsigned long long *>(&a),
                      rb = *reinterpret_cast<unsigned long long *>(&b),
@@ -42,113 +59,98 @@ __device__ __forceinline__ float2 wffma2(float2 a, float2 b, float2 c) {
   return *reinterpret_cast<float2 *>(&rd);
 }
 __device__ __forceinline__ float2 wbc(float v) { return make_float2(v, v); }
-#define WPK(arr, r) (((r)&1) ? (arr)[(r) >> 1].y : (arr)[(r) >> 1].x)
 
 // ================================================================ filter
-// R rays per lane (even), G sphere rows per decision group.
-template <int R, int G, bool CROWS>
-__device__ __forceinline__ void filter_rays(const WaveParams &P, const ConstRows &CR, const uint32_t base,
-                                            const uint32_t stride) {
-  static_assert(R % 2 == 0, "rays are packed in pairs");
-  constexpr int NP = R / 2;
+// @phase filter-prologue
+// Two rays per lane (slots lane and lane + 32), G sphere rows per decision group.  Returns the
+// number of candidate entries the warp recorded (entries beyond the capacity are counted, not stored).
+template <int G, bool CROWS>
+__device__ __forceinline__ uint32_t filter_rays(const WaveParams &P, const ConstRows &CR, WarpState &W,
+                                                uint32_t *glist, const uint32_t lane) {
   const uint32_t npad = P.scene.n_pad;
   const float INF = __int_as_float(0x7f800000);
+  float2 DX, DY, DZ, OX2, OY2, OZ2, NOD, OOT;
   {
-    float2 DX[NP], DY[NP], DZ[NP], OX2[NP], OY2[NP], OZ2[NP], NOD[NP], OOT[NP];
-    uint32_t cnt[R], off[R];  // survivors so far / element offset of the next candidate plane
+    const float4 o0 = W.ro[lane], d0 = W.rd[lane], o1 = W.ro[lane + 32], d1 = W.rd[lane + 32];
+    DX = make_float2(d0.x, d1.x); DY = make_float2(d0.y, d1.y); DZ = make_float2(d0.z, d1.z);
+    OX2 = make_float2(2.0f * o0.x, 2.0f * o1.x); OY2 = make_float2(2.0f * o0.y, 2.0f * o1.y);
+    OZ2 = make_float2(2.0f * o0.z, 2.0f * o1.z);
+    NOD = make_float2(-(o0.x * d0.x + o0.y * d0.y + o0.z * d0.z), -(o1.x * d1.x + o1.y * d1.y + o1.z * d1.z));
+    // idle slots never pass the filter
+    OOT.x = o0.w > 0.0f ? (o0.x * o0.x + o0.y * o0.y + o0.z * o0.z) * (1.0f - RTB_FILTER_SLACK) : INF;
+    OOT.y = o1.w > 0.0f ? (o1.x * o1.x + o1.y * o1.y + o1.z * o1.z) * (1.0f - RTB_FILTER_SLACK) : INF;
+  }
+  uint32_t wcnt = 0;  // entries recorded so far (warp-uniform)
+  const uint32_t lt = (1u << lane) - 1u;
+  const uint32_t e0 = lane << kGroupBits, e1 = (lane + 32u) << kGroupBits;
+  constexpr uint32_t gcap = 64u * kListGlobalPerSlot;
+
+  // @phase main-loop
+  // e = (c.d - o.d)^2 + (2 c.o + w) for one group of G rows; every FFMA2 multiplies by exactly
+  // one sphere scalar (a uniform register when CROWS)
+  auto group = [&](const float4 (&S)[G], float2 (&e)[G]) {
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      off[r] = base + r * stride;
-      const float4 o = P.ray_o[base + r * stride];  // {ox, oy, oz, |d| or < 0 = no ray}
-      const float4 d = P.ray_d[base + r * stride];  // unit direction
-      WPK(DX, r) = d.x; WPK(DY, r) = d.y; WPK(DZ, r) = d.z;
-      WPK(OX2, r) = 2.0f * o.x; WPK(OY2, r) = 2.0f * o.y; WPK(OZ2, r) = 2.0f * o.z;
-      WPK(NOD, r) = -(o.x * d.x + o.y * d.y + o.z * d.z);
-      // idle slots never pass the filter
-      WPK(OOT, r) = o.w > 0.0f ? (o.x * o.x + o.y * o.y + o.z * o.z) * (1.0f - RTB_FILTER_SLACK) : INF;
-      cnt[r] = 0;
+    for (int k = 0; k < G; ++k) {
+      float2 b = wffma2(wbc(S[k].x), DX, wffma2(wbc(S[k].y), DY, wffma2(wbc(S[k].z), DZ, NOD)));
+      float2 e1_ = wffma2(b, b, wbc(S[k].w));
+      e[k] = wffma2(wbc(S[k].x), OX2, wffma2(wbc(S[k].y), OY2, wffma2(wbc(S[k].z), OZ2, e1_)));
     }
-
-    // e = (c.d - o.d)^2 + (2 c.o + w) for one group of G rows; every FFMA2 multiplies by exactly
-    // one sphere scalar (a uniform register when CROWS)
-    auto group = [&](const float4 (&S)[G], float2 (&e)[G][NP]) {
+  };
+  // decision for one group: max over rows, one compare per ray, one vote, one branch
+  auto decide = [&](const float2 (&e)[G], uint32_t s0) {
+    float mx = e[0].x, my = e[0].y;
 #pragma unroll
-      for (int k = 0; k < G; ++k)
-#pragma unroll
-        for (int p = 0; p < NP; ++p) {
-          float2 b = wffma2(wbc(S[k].x), DX[p], wffma2(wbc(S[k].y), DY[p], wffma2(wbc(S[k].z), DZ[p], NOD[p])));
-          float2 e1 = wffma2(b, b, wbc(S[k].w));
-          e[k][p] = wffma2(wbc(S[k].x), OX2[p], wffma2(wbc(S[k].y), OY2[p], wffma2(wbc(S[k].z), OZ2[p], e1)));
-        }
-    };
-    // decision for one group: max over rows, one compare per ray, one vote, one branch
-    uint32_t *const cand = P.cand_idx;
-    const uint32_t nslots = P.n_slots;
-    auto decide = [&](const float2 (&e)[G][NP], uint32_t s0) {
-      float mx[NP], my[NP];
-      bool any = false;
-#pragma unroll
-      for (int p = 0; p < NP; ++p) {
-        mx[p] = e[0][p].x; my[p] = e[0][p].y;
-#pragma unroll
-        for (int k = 1; k < G; ++k) { mx[p] = fmaxf(mx[p], e[k][p].x); my[p] = fmaxf(my[p], e[k][p].y); }
-        any = any | (mx[p] >= OOT[p].x) | (my[p] >= OOT[p].y);  // no short-circuit: independent compares
+    for (int k = 1; k < G; ++k) { mx = fmaxf(mx, e[k].x); my = fmaxf(my, e[k].y); }
+    const bool p0 = mx >= OOT.x, p1 = my >= OOT.y;  // no short-circuit: independent compares
+    if (__any_sync(FULL, p0 | p1)) {
+      // @phase rare
+      // rare path, warp-convergent: the rays whose group maximum passed append ONE entry
+      // {slot, group} each to the warp's list; positions come from two ballots
+      const unsigned b0 = __ballot_sync(FULL, p0), b1 = __ballot_sync(FULL, p1);
+      const uint32_t g = s0 / (uint32_t)G;
+      const uint32_t n0 = __popc(b0);
+      const uint32_t pos0 = wcnt + __popc(b0 & lt), pos1 = wcnt + n0 + __popc(b1 & lt);
+      if (p0) {
+        if (pos0 < kListSmem) W.list[pos0] = e0 | g;
+        else if (pos0 - kListSmem < gcap) glist[pos0 - kListSmem] = e0 | g;
       }
-      if (__any_sync(0xffffffffu, any)) {
-        // rare path, narrowed ray by ray: a ray whose group maximum passed records the group and
-        // the mask of its rows that passed as ONE candidate entry {s0 << kCandShift | mask}
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-          if (((r & 1) ? my[r >> 1] : mx[r >> 1]) >= WPK(OOT, r)) {
-            uint32_t m = 0;
-#pragma unroll
-            for (int k = 0; k < G; ++k) m |= WPK(e[k], r) >= WPK(OOT, r) ? (1u << k) : 0u;
-            if (cnt[r] < kCandPlanes) cand[off[r]] = s0 << kCandShift | m;
-            off[r] += nslots;
-            cnt[r] += 1;
-          }
+      if (p1) {
+        if (pos1 < kListSmem) W.list[pos1] = e1 | g;
+        else if (pos1 - kListSmem < gcap) glist[pos1 - kListSmem] = e1 | g;
       }
-    };
+      wcnt += n0 + __popc(b1);
+      // @phase main-loop
+    }
+  };
 
-    const float4 *frow = P.scene.fast;
-    float4 S[G];
-    float2 ea[G][NP], eb[G][NP];
+  const float4 *frow = P.scene.fast;
+  float4 S[G];
+  float2 ea[G], eb[G];
 #pragma unroll
-    for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[k] : __ldg(frow + k);
+  for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[k] : __ldg(frow + k);
+  group(S, ea);
+#pragma unroll
+  for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[G + k] : __ldg(frow + G + k);
+  uint32_t npad_r = npad;
+  asm volatile("" : "+r"(npad_r));
+  // software pipeline: the FFMA2s of group g+1 are issued before the decision on group g, so
+  // the max/compare/vote/branch chain never sits at the end of a dependency tail.  Two groups
+  // per trip (ea/eb ping-pong).  The row array carries 2G padding rows (w = -inf).
+  for (uint32_t s0 = 0; s0 < npad_r; s0 += 2 * G) {
+    group(S, eb);
+#pragma unroll
+    for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[s0 + 2 * G + k] : __ldg(frow + s0 + 2 * G + k);
+    decide(ea, s0);
     group(S, ea);
 #pragma unroll
-    for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[G + k] : __ldg(frow + G + k);
-    uint32_t npad_r = npad;
-    asm volatile("" : "+r"(npad_r));
-    // software pipeline: the FFMA2s of group g+1 are issued before the decision on group g, so
-    // the max/compare/vote/branch chain never sits at the end of a dependency tail.  Two groups
-    // per trip (ea/eb ping-pong).  The row array carries 2G padding rows (w = -inf).
-    for (uint32_t s0 = 0; s0 < npad_r; s0 += 2 * G) {
-      group(S, eb);
-#pragma unroll
-      for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[s0 + 2 * G + k] : __ldg(frow + s0 + 2 * G + k);
-      decide(ea, s0);
-      group(S, ea);
-#pragma unroll
-      for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[s0 + 3 * G + k] : __ldg(frow + s0 + 3 * G + k);
-      decide(eb, s0 + G);
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) P.cand_cnt[base + r * stride] = cnt[r];
+    for (int k = 0; k < G; ++k) S[k] = CROWS ? CR.row[s0 + 3 * G + k] : __ldg(frow + s0 + 3 * G + k);
+    decide(eb, s0 + G);
   }
+  return wcnt;
 }
 
-template <int R, int G, bool CROWS>
-__global__ void __launch_bounds__(kWBlock, RTW_MINB)
-filter_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
-  const uint32_t stride = P.n_slots / R;  // slot of ray r = base + r * stride
-  // warp-uniform trip count (stride is a multiple of the block size): the sphere loop must stay
-  // convergent so that its rows can live in uniform registers
-  for (uint32_t blk = blockIdx.x; blk < stride / kWBlock; blk += gridDim.x)
-    filter_rays<R, G, CROWS>(P, CR, blk * kWBlock + threadIdx.x, stride);
-}
-
-// ================================================================ shade
+// ================================================================ resolve
+// @phase resolve
 // sqrt of a non-negative double: rsqrt seed in f32, two Newton steps in f64 (no f64 division)
 __device__ __forceinline__ double wave_dsqrt(double x) {
   float xf = fmaxf((float)x, 1e-30f);
@@ -160,22 +162,31 @@ __device__ __forceinline__ double wave_dsqrt(double x) {
   return s;
 }
 
-struct WRay {
-  double ox, oy, oz, dx, dy, dz, a, tminA;
-  double lo;  // smallest acceptable root numerator: tminA, or the next double above it when strict
-};
 __device__ __forceinline__ double next_up_pos(double x) {  // x > 0 finite
   return __longlong_as_double(__double_as_longlong(x) + 1ll);
 }
 
-// sphere::hit on numerators (root = N / a, a common to the ray): src/cpu/sphere.h:24-51 with the
-// inclusive upper bound of hittable_list.h:34-39 (a later sphere with an equal root wins), or —
-// strict — the v4 interval of src/gpu/sphere.h:31-36 (t_min < root < t_max: the earlier sphere
-// wins).  Both are ONE pair of compares, N < lo || !(N < hi): the bounds carry the rule
-// (lo = t_min or the next double above it; hi = the best root, or the next double above it when
-// an equal root may replace it).
-__device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, double &bestN,
-                                               double &hi, const bool strict) {
+// A ray as the exact test sees it: f32 origin and unit direction widened to double.
+struct WRay {
+  double ox, oy, oz, dx, dy, dz, a;
+  double lo;  // smallest acceptable root numerator: t_min * a, or the next double above it when strict
+};
+__device__ __forceinline__ WRay widen_ray(const float4 o, const float4 d, const bool strict) {
+  WRay r;
+  r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
+  r.a = r.dx * r.dx + r.dy * r.dy + r.dz * r.dz;
+  const double tminA = 0.001 * (double)o.w * r.a;  // main.cc:19 t_min in unit-direction units, times a
+  r.lo = strict ? next_up_pos(tminA) : tminA;
+  return r;
+}
+
+// sphere::hit on numerators (root = N / a, a common to the ray), src/cpu/sphere.h:24-51, in the
+// order-independent form: the root a sphere offers is its near root if that lies in the interval,
+// else its far root (a far root can only be accepted when the near one lies before t_min, since
+// near <= far); the closest-hit record then keeps the smallest root and, among equal roots, the
+// LATER sphere (inclusive upper bound of hittable_list.h:34-39 + sphere.h:38-40) -- or, strict, the
+// EARLIER one (the v4 interval of src/gpu/sphere.h:31-36: t_min < root < t_max).
+__device__ __forceinline__ bool exact_root(const double4 S, const WRay &r, unsigned long long &key) {
   double ocx = r.ox - S.x, ocy = r.oy - S.y, ocz = r.oz - S.z;
   double half_b = ocx * r.dx + ocy * r.dy + ocz * r.dz;
   double c = ocx * ocx + ocy * ocy + ocz * ocz - S.w * S.w;
@@ -183,132 +194,174 @@ __device__ __forceinline__ bool wave_exact_hit(const double4 S, const WRay &r, d
   if (disc < 0.0) return false;
   double sq = wave_dsqrt(disc);
   double N = -half_b - sq;
-  if (N < r.lo || !(N < hi)) {
+  if (N < r.lo) {
     N = -half_b + sq;
-    if (N < r.lo || !(N < hi)) return false;
+    if (N < r.lo) return false;
   }
-  bestN = N;
-  hi = strict ? N : next_up_pos(N);
+  key = (unsigned long long)__double_as_longlong(N);
   return true;
 }
 
-// One slot, one wave.  (1) Finish the ray segment traced by the last filter pass: f64 resolution
-// of its candidates, sky on a miss.  (2) ONE Philox block per slot and wave: the camera sample of
+// RT_FLAG_F32_HIT: sphere::hit in f32 on the reference's un-normalised direction, op for op
+// src/gpu/sphere.h:15-47 (no self-skip, f32 hit point) -- reproduces the cancellation of
+// |oc|^2 - r^2 on the r = 1000 ground sphere that the reference's CUDA program shows.  The key is
+// the bit pattern of the (positive) f32 root.
+__device__ __forceinline__ bool exact_root_f32(const double4 S, const float4 o, const float4 d,
+                                               const bool strict, unsigned long long &key) {
+  const float ddx = d.x * o.w, ddy = d.y * o.w, ddz = d.z * o.w;
+  const float a = ddx * ddx + ddy * ddy + ddz * ddz;
+  const float r = (float)S.w;
+  const float ocx = o.x - (float)S.x, ocy = o.y - (float)S.y, ocz = o.z - (float)S.z;
+  const float hb = ocx * ddx + ocy * ddy + ocz * ddz;
+  const float c = ocx * ocx + ocy * ocy + ocz * ocz - r * r;
+  const float disc = hb * hb - a * c;
+  if (disc < 0.0f) return false;
+  const float sq = __fsqrt_rn(disc);  // IEEE like the reference's build (this TU uses approximate / and sqrt)
+  float root = __fdiv_rn(-hb - sq, a);
+  if (strict ? !(0.001f < root) : root < 0.001f) {
+    root = __fdiv_rn(-hb + sq, a);
+    if (strict ? !(0.001f < root) : root < 0.001f) return false;
+  }
+  key = (unsigned long long)__float_as_uint(root);
+  return true;
+}
+
+// closest-hit record of a slot <- one accepted root (called by one lane per slot at a time)
+__device__ __forceinline__ void record_root(WarpState &W, const uint32_t slot, const unsigned long long key,
+                                            const int s, const bool strict) {
+  const unsigned long long cur = W.key[slot];
+  const int cid = W.id[slot];
+  if (key < cur || (key == cur && (strict ? s < cid : s > cid))) {
+    W.key[slot] = key;
+    W.id[slot] = s;
+  }
+}
+
+// The warp walks its candidate list 32 entries at a time.  An entry names a slot and a decision
+// group; the lane re-runs the f32 test on the group's G rows (same arithmetic as the filter), then
+// one exact test per round on the rows that pass.  Lanes that hold accepted roots of the SAME
+// slot in a round update its record one after the other (a single turn almost always).
+template <int G, bool F32HIT>
+__device__ __forceinline__ void resolve_entries(const WaveParams &P, WarpState &W, const uint32_t *glist,
+                                                const uint32_t n_entries, const double4 *exact,
+                                                const uint32_t lane) {
+  const bool strict = P.model_v4 != 0u;
+  const float4 *fast = P.scene.fast;
+  const uint32_t lt = (1u << lane) - 1u;
+  for (uint32_t first = 0; first < n_entries; first += 32) {  // warp-uniform trip count
+    const uint32_t idx = first + lane;
+    uint32_t m = 0, slot = 0, s0 = 0;
+    float4 o = make_float4(0.f, 0.f, 0.f, -1.f), d = make_float4(0.f, 1.f, 0.f, 0.f);
+    if (idx < n_entries) {
+      const uint32_t ent = idx < kListSmem ? W.list[idx] : glist[idx - kListSmem];
+      slot = ent >> kGroupBits;
+      s0 = (ent & ((1u << kGroupBits) - 1u)) * (uint32_t)G;
+      o = W.ro[slot];
+      d = W.rd[slot];
+      const uint32_t skip = (uint32_t)__float_as_int(d.w);  // the sphere the ray just left, or -1
+      const float nod = -(o.x * d.x + o.y * d.y + o.z * d.z);
+      const float ox2 = 2.0f * o.x, oy2 = 2.0f * o.y, oz2 = 2.0f * o.z;
+      const float oot = (o.x * o.x + o.y * o.y + o.z * o.z) * (1.0f - RTB_FILTER_SLACK);
+#pragma unroll
+      for (int k = 0; k < G; ++k) {
+        const float4 S = __ldg(fast + s0 + k);
+        const float b = fmaf(S.x, d.x, fmaf(S.y, d.y, fmaf(S.z, d.z, nod)));
+        const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
+        if (e >= oot && s0 + (uint32_t)k != skip) m |= 1u << k;
+      }
+    }
+    const WRay ray = widen_ray(o, d, strict);
+    while (__any_sync(FULL, m != 0u)) {
+      bool hit = false;
+      unsigned long long key = 0;
+      int s = -1;
+      if (m) {
+        s = (int)(s0 + (uint32_t)__ffs((int)m) - 1u);
+        m &= m - 1u;
+        hit = F32HIT ? exact_root_f32(exact[s], o, d, strict, key) : exact_root(exact[s], ray, key);
+      }
+      // lanes with accepted roots of one slot take turns (lanes without one match nobody)
+      const unsigned peers = __match_any_sync(FULL, hit ? slot : 64u + lane);
+      const uint32_t turn = __popc(peers & lt);
+      const uint32_t turns = __reduce_max_sync(FULL, turn);
+      for (uint32_t t = 0; t <= turns; ++t) {
+        if (hit && turn == t) record_root(W, slot, key, s, strict);
+        __syncwarp();
+      }
+    }
+  }
+}
+
+// Fallback: every lane scans ALL spheres for its own two slots.  Taken when the warp's candidate
+// list overflowed (rays along long rows of spheres) -- with the f32 test first -- and under
+// RT_FLAG_NO_FILTER, without it: hittable_list::hit as written (hittable_list.h:28-43).
+template <bool F32HIT>
+__device__ __forceinline__ void resolve_scan(const WaveParams &P, WarpState &W, const double4 *exact,
+                                             const uint32_t lane) {
+  const bool strict = P.model_v4 != 0u;
+  const float4 *fast = P.scene.fast;
+#pragma unroll 1
+  for (int r = 0; r < 2; ++r) {
+    const uint32_t slot = lane + 32u * r;
+    const float4 o = W.ro[slot], d = W.rd[slot];
+    if (!(o.w > 0.0f)) continue;
+    const uint32_t skip = (uint32_t)__float_as_int(d.w);
+    const float nod = -(o.x * d.x + o.y * d.y + o.z * d.z);
+    const float ox2 = 2.0f * o.x, oy2 = 2.0f * o.y, oz2 = 2.0f * o.z;
+    const float oot = (o.x * o.x + o.y * o.y + o.z * o.z) * (1.0f - RTB_FILTER_SLACK);
+    const WRay ray = widen_ray(o, d, strict);
+    for (uint32_t s = 0; s < P.scene.n; ++s) {
+      if (!P.no_filter) {
+        const float4 S = __ldg(fast + s);
+        const float b = fmaf(S.x, d.x, fmaf(S.y, d.y, fmaf(S.z, d.z, nod)));
+        const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
+        if (!(e >= oot)) continue;
+      }
+      if (s == skip) continue;
+      unsigned long long key;
+      if (F32HIT ? exact_root_f32(exact[s], o, d, strict, key) : exact_root(exact[s], ray, key))
+        record_root(W, slot, key, (int)s, strict);
+    }
+  }
+}
+
+// ================================================================ shade
+// @phase fetch
+// q / d and q % d for quotients below 2^16: float estimate (within 1), fixed up exactly
+__device__ __forceinline__ void divmod_small(const uint32_t q, const uint32_t d, uint32_t &quo, uint32_t &rem) {
+  uint32_t e = (uint32_t)(__uint2float_rz(q) * __frcp_rn(__uint2float_rn(d)));
+  int r = (int)(q - e * d);
+  if (r < 0) { e -= 1u; r += (int)d; }
+  else if ((uint32_t)r >= d) { e += 1u; r -= (int)d; }
+  quo = e; rem = (uint32_t)r;
+}
+
+// One slot, one wave.  (1) Finish the ray segment traced by the last wave from the slot's
+// closest-hit record: sky on a miss.  (2) ONE Philox block per slot and wave: the camera sample of
 // a new path (miss / empty slot) or the scatter sample of the hit.  (3) camera::get_ray or
 // material::scatter.  A path that ends at a hit (absorbed, bounce limit) leaves the slot without a
 // ray for one wave and regenerates in the next one.  Returns 0 once the slot is retired.
-template <bool BVH, bool F32HIT = false>
-__device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32_t i,
-                                               const double4 *exact, const float4 *mat,
+template <bool F32HIT>
+__device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, WarpState &W, const uint32_t slot,
+                                               const uint32_t i, const double4 *exact, const float4 *mat,
                                                const float2 *aux, const uint32_t npix,
-                                               const uint64_t total_items) {
+                                               const uint32_t total_items) {
+  // @phase slot-state
   float4 T = P.thr[i];  // {tr, tg, tb, depth}
   int depth = __float_as_int(T.w);
   if (depth < 0) return 0u;  // slot retired: the frame's work queue is empty
-  uint4 st = P.it[i];   // {item = slice << kItemShift | pixel (0xffffffff = none), samp, samp_end, -}
+  uint4 st = P.it[i];   // {item = slice << kItemShift | pixel (kNoItem = none), samp, samp_end, -}
   float4 A = P.acc[i];  // {sum r, sum g, sum b, ray segments} of the slot's item
   float4 RO = make_float4(0.f, 0.f, 0.f, -1.f), RD = make_float4(0.f, 1.f, 0.f, 0.f);
   int id = -1;
   double hpx = 0, hpy = 0, hpz = 0;  // hit point (f64)
 
   if (depth > 0) {
-    // ---------------------------------------------------------- resolve
-    RO = P.ray_o[i];
-    RD = P.ray_d[i];
+    // @phase sky-hitpoint
+    RO = W.ro[slot];
+    RD = W.rd[slot];
     A.w += 1.0f;  // one ray_color invocation (src/cpu/main.cc:12)
-    WRay ray;
-    ray.ox = RO.x; ray.oy = RO.y; ray.oz = RO.z; ray.dx = RD.x; ray.dy = RD.y; ray.dz = RD.z;
-    ray.a = ray.dx * ray.dx + ray.dy * ray.dy + ray.dz * ray.dz;
-    ray.tminA = 0.001 * (double)RO.w * ray.a;  // main.cc:19 t_min in unit-direction units, times a
-    double bestN = __longlong_as_double(0x7ff0000000000000ll);
-    double hi = bestN;
-    if (BVH) {
-      // the traversal already resolved the closest hit: {id, numerator of the root}
-      id = (int)P.cand_idx[i];
-      bestN = __hiloint2double((int)P.cand_idx[(size_t)2 * P.n_slots + i],
-                               (int)P.cand_idx[(size_t)1 * P.n_slots + i]);
-    } else if (F32HIT) {
-      // RT_FLAG_F32_HIT: sphere::hit in f32 on the reference's un-normalised direction, op for op
-      // src/gpu/sphere.h:15-47 (no self-skip, f32 hit point) -- reproduces the cancellation of
-      // |oc|^2 - r^2 on the r = 1000 ground sphere that the reference's CUDA program shows
-      const uint32_t cnt = P.cand_cnt[i];
-      const bool strict = P.model_v4 != 0u;
-      const float ddx = RD.x * RO.w, ddy = RD.y * RO.w, ddz = RD.z * RO.w;
-      const float a = ddx * ddx + ddy * ddy + ddz * ddz;
-      float bestT = __int_as_float(0x7f800000);
-      auto hit32 = [&](const uint32_t s) {
-        const double4 S = exact[s];
-        const float r = (float)S.w;
-        const float ocx = RO.x - (float)S.x, ocy = RO.y - (float)S.y, ocz = RO.z - (float)S.z;
-        const float hb = ocx * ddx + ocy * ddy + ocz * ddz;
-        const float c = ocx * ocx + ocy * ocy + ocz * ocz - r * r;
-        const float disc = hb * hb - a * c;
-        if (disc < 0.0f) return;
-        const float sq = __fsqrt_rn(disc);  // IEEE like the reference's build (this TU uses approximate / and sqrt)
-        float root = __fdiv_rn(-hb - sq, a);
-        if (strict ? !(0.001f < root && root < bestT) : (root < 0.001f || bestT < root)) {
-          root = __fdiv_rn(-hb + sq, a);
-          if (strict ? !(0.001f < root && root < bestT) : (root < 0.001f || bestT < root)) return;
-        }
-        bestT = root;
-        id = (int)s;
-      };
-      if (cnt <= kCandPlanes) {
-        uint32_t k = 0, m = 0, s0 = 0;
-        for (;;) {
-          if (m == 0u) {
-            if (k == cnt) break;
-            const uint32_t e = P.cand_idx[(size_t)k * P.n_slots + i];
-            ++k;
-            s0 = e >> kCandShift;
-            m = e & ((1u << kCandShift) - 1u);
-          }
-          hit32(s0 + (uint32_t)__ffs((int)m) - 1u);
-          m &= m - 1u;
-        }
-      } else {
-        for (uint32_t s = 0; s < P.scene.n; ++s) hit32(s);
-      }
-      if (id >= 0) {  // ray::at in f32 (src/gpu/ray.h), kept as the slot's f64 hit point
-        hpx = (double)fmaf(bestT, ddx, RO.x); hpy = (double)fmaf(bestT, ddy, RO.y); hpz = (double)fmaf(bestT, ddz, RO.z);
-      }
-    } else {
-      const uint32_t cnt = P.cand_cnt[i];
-      const bool strict = P.model_v4 != 0u;
-      ray.lo = strict ? next_up_pos(ray.tminA) : ray.tminA;
-      const uint32_t skip = (uint32_t)__float_as_int(RD.w);  // the sphere the ray just left, or -1
-      if (cnt <= kCandPlanes) {
-        // entries {first row of a group << kCandShift | mask of its rows that passed}, ascending;
-        // one exact test per trip so that lanes with different entry shapes stay together
-        uint32_t k = 0, m = 0, s0 = 0;
-        for (;;) {
-          if (m == 0u) {
-            if (k == cnt) break;
-            const uint32_t e = P.cand_idx[(size_t)k * P.n_slots + i];
-            ++k;
-            s0 = e >> kCandShift;
-            m = e & ((1u << kCandShift) - 1u);
-          }
-          const uint32_t s = s0 + (uint32_t)__ffs((int)m) - 1u;
-          m &= m - 1u;
-          if (s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
-        }
-      } else {
-        // candidate planes overflowed (a ray along a long row of spheres): scan every sphere, the
-        // same conservative f32 test first so that f64 work is spent on its survivors only
-        const float nod = -(RO.x * RD.x + RO.y * RD.y + RO.z * RD.z);
-        const float ox2 = 2.0f * RO.x, oy2 = 2.0f * RO.y, oz2 = 2.0f * RO.z;
-        const float oot = (RO.x * RO.x + RO.y * RO.y + RO.z * RO.z) * (1.0f - RTB_FILTER_SLACK);
-        const float4 *fast = P.scene.fast;
-        for (uint32_t s = 0; s < P.scene.n; ++s) {
-          const float4 S = __ldg(fast + s);
-          const float b = fmaf(S.x, RD.x, fmaf(S.y, RD.y, fmaf(S.z, RD.z, nod)));
-          const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
-          // RT_FLAG_NO_FILTER: no pre-test at all -- hittable_list::hit as written (hittable_list.h:28-43)
-          if ((e >= oot || P.no_filter) && s != skip && wave_exact_hit(exact[s], ray, bestN, hi, strict)) id = (int)s;
-        }
-      }
-    }
+    id = W.id[slot];
     if (id < 0) {
       // sky, src/cpu/main.cc:27-29 (direction already unit length)
       float t = 0.5f * (RD.y + 1.0f);
@@ -317,19 +370,28 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       A.y += T.y * (w + t * 0.7f);
       A.z += T.z * (w + t * 1.0f);
       depth = 0;
-    } else if (!F32HIT) {
-      const double t = bestN * (2.0 - ray.a);  // 1/a = 2 - a to within eps^2 (a = 1 + eps)
-      hpx = ray.ox + t * ray.dx; hpy = ray.oy + t * ray.dy; hpz = ray.oz + t * ray.dz;
+    } else if (F32HIT) {
+      // ray::at in f32 (src/gpu/ray.h), kept as the slot's f64 hit point
+      const float bestT = __uint_as_float((uint32_t)W.key[slot]);
+      const float ddx = RD.x * RO.w, ddy = RD.y * RO.w, ddz = RD.z * RO.w;
+      hpx = (double)fmaf(bestT, ddx, RO.x); hpy = (double)fmaf(bestT, ddy, RO.y); hpz = (double)fmaf(bestT, ddz, RO.z);
+    } else {
+      const double bestN = __longlong_as_double((long long)W.key[slot]);
+      const double ox = RO.x, oy = RO.y, oz = RO.z, dx = RD.x, dy = RD.y, dz = RD.z;
+      const double a = dx * dx + dy * dy + dz * dz;
+      const double t = bestN * (2.0 - a);  // 1/a = 2 - a to within eps^2 (a = 1 + eps)
+      hpx = ox + t * dx; hpy = oy + t * dy; hpz = oz + t * dz;
     }
   }
 
   const bool regen = depth == 0;
   if (regen) {
+    // @phase fetch
     // ------------------------------------------------------------ next sample / next item
     while (st.y == st.z) {  // item exhausted: flush it and fetch the next
-      if (st.x != 0xffffffffu) {
+      if (st.x != kNoItem) {
         P.accum[(size_t)(st.x >> kItemShift) * npix + (st.x & kItemPixelMask)] = A;
-        st.x = 0xffffffffu;
+        st.x = kNoItem;
       }
       // warp-aggregated pop: the lanes that need an item right now share ONE atomic (single-address
       // atomics top out near 1 G/s, and a frame ends on one-sample items)
@@ -339,52 +401,31 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       unsigned long long itq = 0;
       if ((int)lane == leader) itq = atomicAdd(P.counter, (unsigned long long)__popc(am));
       itq = __shfl_sync(am, itq, leader) + (unsigned long long)__popc(am & ((1u << lane) - 1u));
-      if (itq >= total_items) { depth = -1; break; }
+      if (itq >= (unsigned long long)total_items) { depth = -1; break; }
       // hand-out order: first every slice of the heavy pixels, then the other pixels slice by
-      // slice (largest slices first, heaviest pixels first within a slice)
-      uint32_t ord, px;
-      if (total_items <= 0xffffffffull) {
-        // 32-bit arithmetic (a 64-bit division is ~100 instructions at a few active lanes)
-        const uint32_t q32 = (uint32_t)itq;
-        if (P.order) {
-          const uint32_t nh = __ldg(P.heavy);
-          const uint32_t heavy_items = nh * P.n_orders;
-          if (q32 < heavy_items) {
-            ord = q32 / nh;
-            px = __ldg(P.order + (q32 - ord * nh));
-          } else {
-            const uint32_t q = q32 - heavy_items, nl = npix - nh;
-            ord = q / nl;
-            px = __ldg(P.order + nh + (q - ord * nl));
-          }
-        } else {
-          ord = q32 / npix;
-          px = q32 - ord * npix;
-        }
-      } else if (P.order) {
+      // slice (largest slices first, heaviest pixels first within a slice).  The queue holds fewer
+      // than 2^32 items (2^26 pixels x 64 slices), quotients are slice positions (< 64).
+      uint32_t q = (uint32_t)itq, ord, px;
+      if (P.order) {
         const uint32_t nh = __ldg(P.heavy);
-        const uint64_t heavy_items = (uint64_t)nh * P.n_orders;
-        if (itq < heavy_items) {
-          ord = (uint32_t)(itq / nh);
-          px = __ldg(P.order + (uint32_t)(itq - (uint64_t)ord * nh));
-        } else {
-          const uint64_t q = itq - heavy_items;
-          const uint32_t nl = npix - nh;
-          ord = (uint32_t)(q / nl);
-          px = __ldg(P.order + nh + (uint32_t)(q - (uint64_t)ord * nl));
-        }
+        const uint32_t heavy_items = nh * P.n_orders;
+        uint32_t dvs = nh, off = 0;
+        if (q >= heavy_items) { q -= heavy_items; dvs = npix - nh; off = nh; }
+        divmod_small(q, dvs, ord, px);
+        px = __ldg(P.order + off + px);
       } else {
-        ord = (uint32_t)(itq / npix);
-        px = (uint32_t)(itq - (uint64_t)ord * npix);
+        divmod_small(q, npix, ord, px);
       }
-      const uint32_t sl = slice_in_order(ord, P.slice_begin, P.slice_end);
+      const uint32_t sl = P.order_slice[ord];
       st.x = sl << kItemShift | px;
-      slice_range(sl, P.spp, st.y, st.z);
+      st.y = P.slice_bounds[sl];
+      st.z = P.slice_bounds[sl + 1u];
       A = make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
 
   if (depth >= 0) {
+    // @phase philox
     // ------------------------------------------------------------ the wave's random numbers
     // stream: key = (pixel, sample), counter slot 0 = camera, k >= 1 = scatter at the k-th hit
     const uint32_t px = st.x & kItemPixelMask;
@@ -392,8 +433,10 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
     const float4 xi = philox_uniforms(px, P.sample_offset + (regen ? st.y : st.y - 1u),
                                       regen ? 0u : hitno, P.seed);
     if (regen) {
+      // @phase camera
       // camera::get_ray (src/cpu/camera.h:28-35) with pixel jitter (main.cc:116-117)
-      const uint32_t row = px / P.width, ii = px - row * P.width;
+      uint32_t row, ii;
+      divmod_small(px, P.width, row, ii);  // rows < 2^16 (checked by rt_frame_create)
       const uint32_t j = P.height - 1 - row;
       st.y += 1;
       float u = ((float)ii + xi.x) * P.cam.inv_wm1;
@@ -417,6 +460,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
       T.x = T.y = T.z = 1.0f;
       depth = (int)P.max_depth;
     } else {
+      // @phase scatter
       // hit record, src/cpu/sphere.h:43-48 + hittable.h:16-19: point in f64, then narrowed
       const float dx = RD.x, dy = RD.y, dz = RD.z;
       const double4 S = exact[id];
@@ -492,8 +536,11 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
     RO.w = -1.0f;
   }
 
-  P.ray_o[i] = RO;
-  if (depth > 0) P.ray_d[i] = RD;
+  // @phase slot-state
+  W.ro[slot] = RO;
+  if (depth > 0) W.rd[slot] = RD;
+  W.key[slot] = kInfKey;
+  W.id[slot] = -1;
   T.w = __int_as_float(depth);
   P.thr[i] = T;
   P.acc[i] = A;
@@ -501,6 +548,7 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, const uint32
   return depth >= 0 ? 1u : 0u;  // still part of the frame (with or without a ray this wave)
 }
 
+// @phase stage
 // per-hit scene rows -> shared memory: 1-D bulk (TMA) copies completing on an mbarrier
 __device__ __forceinline__ void stage_hit_rows(const WaveParams &P, unsigned char *smem_raw,
                                                uint64_t *bar, const double4 *&exact,
@@ -529,52 +577,28 @@ __device__ __forceinline__ void stage_hit_rows(const WaveParams &P, unsigned cha
   exact = s_exact; mat = s_mat; aux = s_aux;
 }
 
-template <bool SMEM>
-__global__ void __launch_bounds__(256, 4)
-shade_kernel(const __grid_constant__ WaveParams P) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t s_bar;
-  const double4 *exact = P.scene.exact;
-  const float4 *mat = P.scene.mat;
-  const float2 *aux = P.scene.aux;
-  if (SMEM) stage_hit_rows(P, smem_raw, &s_bar, exact, mat, aux);
-  const uint32_t npix = P.width * P.height;
-  const uint64_t total_items = (uint64_t)npix * P.n_orders;
-  uint32_t live_lanes = 0;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_slots; i += gridDim.x * blockDim.x)
-    live_lanes += shade_slot<false>(P, i, exact, mat, aux, npix, total_items);
-  // live rays of the next wave (the host stops the frame when this stays 0)
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) live_lanes += __shfl_xor_sync(0xffffffffu, live_lanes, o);
-  if ((threadIdx.x & 31) == 0 && live_lanes) atomicAdd(P.live, live_lanes);
-}
-
 // ================================================================ BVH traversal (optional mode)
-// Closest hit of R rays through the host-built hierarchy (rt_bvh.cu) with the REFERENCE's result:
-// the linear scan of hittable_list::hit accepts sphere s when its root N_s (near root if >= t_min,
-// else far root) is <= the best so far, so the winner is the smallest root and, among equal roots,
-// the LARGEST index (sphere.h:38-40 + hittable_list.h:34-39).  That rule does not depend on the
-// visiting order, so leaves may be visited in any order.  Boxes are tested in f32 with outward
-// slack; a node is skipped only if it lies entirely beyond the best root or before t_min.
-// Writes {id, root numerator} to candidate planes 0..2 of the slot.
-template <int R>
-__device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *exact, const uint32_t base,
-                                          const uint32_t stride) {
+// @phase bvh
+// Closest hit of the lane's two rays through the host-built hierarchy (rt_bvh.cu) with the
+// REFERENCE's result: the linear scan of hittable_list::hit keeps the smallest root and, among
+// equal roots, the LARGEST index (sphere.h:38-40 + hittable_list.h:34-39) -- a rule that does not
+// depend on the visiting order, so leaves may be visited in any order.  Boxes are tested in f32
+// with outward slack; a node is skipped only if it lies entirely beyond the best root or before
+// t_min.  Writes the slot's closest-hit record.
+__device__ __forceinline__ void bvh_trace(const WaveParams &P, WarpState &W, const double4 *exact,
+                                          const uint32_t lane) {
   const BvhNode *nodes = P.scene.bvh_nodes;
   const uint32_t *prim = P.scene.bvh_prim;
   const float4 *fast = P.scene.fast;
   const bool strict = P.model_v4 != 0u;
 #pragma unroll 1
-  for (int r = 0; r < R; ++r) {
-    const uint32_t slot = base + r * stride;
-    const float4 o = P.ray_o[slot];
+  for (int r = 0; r < 2; ++r) {
+    const uint32_t slot = lane + 32u * r;
+    const float4 o = W.ro[slot];
     if (!(o.w > 0.0f)) continue;  // no ray this wave
-    const float4 d = P.ray_d[slot];
-    WRay ray;
-    ray.ox = o.x; ray.oy = o.y; ray.oz = o.z; ray.dx = d.x; ray.dy = d.y; ray.dz = d.z;
-    ray.a = ray.dx * ray.dx + ray.dy * ray.dy + ray.dz * ray.dz;
-    ray.tminA = 0.001 * (double)o.w * ray.a;
-    double bestN = __longlong_as_double(0x7ff0000000000000ll);
+    const float4 d = W.rd[slot];
+    const WRay ray = widen_ray(o, d, strict);
+    unsigned long long best = kInfKey;
     int id = -1;
     const uint32_t skip = (uint32_t)__float_as_int(d.w);
     const float tmin_f = 0.001f * o.w * 0.9999f;
@@ -616,26 +640,11 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
           const float b = fmaf(S.x, d.x, fmaf(S.y, d.y, fmaf(S.z, d.z, nod)));
           const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
           if (e >= oot) {
-            const double4 E = exact[s];
-            double ocx = ray.ox - E.x, ocy = ray.oy - E.y, ocz = ray.oz - E.z;
-            double half_b = ocx * ray.dx + ocy * ray.dy + ocz * ray.dz;
-            double c = ocx * ocx + ocy * ocy + ocz * ocz - E.w * E.w;
-            double disc = half_b * half_b - ray.a * c;
-            if (disc >= 0.0) {
-              double sq = wave_dsqrt(disc);
-              double N = -half_b - sq;
-              bool take;
-              if (strict) {  // v4: t_min < root, equal roots keep the SMALLER index
-                if (N <= ray.tminA) N = -half_b + sq;
-                take = N > ray.tminA && (N < bestN || (N == bestN && (int)s < id));
-              } else {
-                if (N < ray.tminA) N = -half_b + sq;
-                take = N >= ray.tminA && (N < bestN || (N == bestN && (int)s > id));
-              }
-              if (take) {
-                bestN = N; id = (int)s;
-                tbest = (float)(N * 1.00001) + 1e-6f;
-              }
+            unsigned long long key;
+            if (exact_root(exact[s], ray, key) &&
+                (key < best || (key == best && (strict ? (int)s < id : (int)s > id)))) {
+              best = key; id = (int)s;
+              tbest = (float)(__longlong_as_double((long long)key) * 1.00001) + 1e-6f;
             }
           }
         }
@@ -659,188 +668,91 @@ __device__ __forceinline__ void bvh_trace(const WaveParams &P, const double4 *ex
         }
       }
     }
-    P.cand_idx[slot] = (uint32_t)id;
-    P.cand_idx[(size_t)1 * P.n_slots + slot] = (uint32_t)__double2loint(bestN);
-    P.cand_idx[(size_t)2 * P.n_slots + slot] = (uint32_t)__double2hiint(bestN);
+    W.key[slot] = best;
+    W.id[slot] = id;
   }
 }
 
-// ================================================================ fused persistent form
-// Every lane owns R slots for the whole frame and alternates shade (one slot at a time, rolled
-// loop, state in the pool) and filter (R rays at once, registers hold nothing but rays).  No
-// kernel boundary, no inter-lane dependency; warps of an SM drift apart, so the latency-bound
-// shade phases of some warps overlap the FMA-pipe-bound filter phases of the others.
-// CTAs per SM: the brute-force form needs its 78 registers (3 x 256 threads); the BVH form fits 64
-// and is bound by load latency, so it takes a fourth CTA.
+// ================================================================ the persistent kernel
+// @phase kernel-top
+// CTAs per SM: the brute-force form needs its registers for the filter loop (3 x 256 threads); the
+// BVH form is bound by load latency and takes a fourth CTA.
 constexpr int kBvhMinB = RTW_MINB + 1;
-template <int R, int G, bool CROWS, bool SMEM, bool BVH, bool F32HIT = false>
+template <int G, bool CROWS, bool SMEM, bool BVH, bool F32HIT = false>
 __global__ void __launch_bounds__(kWBlock, BVH ? kBvhMinB : RTW_MINB)
 fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t s_bar;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  WarpState &W = reinterpret_cast<WarpState *>(smem_raw)[warp];
   const double4 *exact = P.scene.exact;
   const float4 *mat = P.scene.mat;
   const float2 *aux = P.scene.aux;
-  if (SMEM) stage_hit_rows(P, smem_raw, &s_bar, exact, mat, aux);
+  if (SMEM) stage_hit_rows(P, smem_raw + kWarps * sizeof(WarpState), &s_bar, exact, mat, aux);
   const uint32_t npix = P.width * P.height;
-  const uint64_t total_items = (uint64_t)npix * P.n_orders;
-  const uint32_t stride = P.n_slots / R;
+  const uint32_t total_items = npix * P.n_orders;  // < 2^32: 2^26 pixels x 64 slices at most
+  const uint32_t stride = P.n_slots / 2u;
   const uint32_t base = blockIdx.x * kWBlock + threadIdx.x;  // grid * block == stride
+  uint32_t *glist = P.glist + (size_t)(blockIdx.x * kWarps + warp) * (64u * kListGlobalPerSlot);
 #pragma unroll 1
-  for (int r = 0; r < R; ++r) {
-    const uint32_t i = base + r * stride;
+  for (int r = 0; r < 2; ++r) {
+    const uint32_t i = base + r * stride, slot = lane + 32u * r;
     P.thr[i] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));  // depth 0: needs a path
     P.acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    P.it[i] = make_uint4(0xffffffffu, 0u, 0u, 0u);
+    P.it[i] = make_uint4(kNoItem, 0u, 0u, 0u);
+    W.ro[slot] = make_float4(0.f, 0.f, 0.f, -1.f);
+    W.rd[slot] = make_float4(0.f, 1.f, 0.f, __int_as_float(-1));
+    W.key[slot] = kInfKey;
+    W.id[slot] = -1;
   }
   for (;;) {
     uint32_t live = 0;
 #pragma unroll 1
-    for (int r = 0; r < R; ++r) live += shade_slot<BVH, F32HIT>(P, base + r * stride, exact, mat, aux, npix, total_items);
-#ifdef RTW_CTA_SYNC
-    // CTA-wide barrier + vote: the warps of a CTA walk the sphere rows in step (one stream of
-    // constant-cache lines per CTA instead of one per warp)
-    if (!__syncthreads_or(live != 0u)) break;
-#else
-    if (__all_sync(0xffffffffu, live == 0u)) break;  // warp-uniform exit keeps the loop convergent
-#endif
-    if (BVH) bvh_trace<R>(P, exact, base, stride);
-    else if (P.no_filter) {
-      // soundness switch: no candidates are recorded, every slot takes the full-scan branch
-#pragma unroll
-      for (int r = 0; r < R; ++r) P.cand_cnt[base + r * stride] = kCandPlanes + 1u;
-    } else filter_rays<R, G, CROWS>(P, CR, base, stride);
-  }
-}
-
-__global__ void __launch_bounds__(256) wave_init_kernel(const __grid_constant__ WaveParams P) {
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < P.n_slots; i += gridDim.x * blockDim.x) {
-    P.thr[i] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));  // depth 0: needs a path
-    P.acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    P.it[i] = make_uint4(0xffffffffu, 0u, 0u, 0u);
-    P.ray_o[i] = make_float4(0.f, 0.f, 0.f, -1.0f);
-    P.ray_d[i] = make_float4(0.f, 1.f, 0.f, 0.f);
-    P.cand_cnt[i] = 0;
+    for (int r = 0; r < 2; ++r)
+      live += shade_slot<F32HIT>(P, W, lane + 32u * r, base + r * stride, exact, mat, aux, npix, total_items);
+    if (__all_sync(FULL, live == 0u)) break;  // warp-uniform exit keeps the loop convergent
+    __syncwarp();  // the wave's rays and the cleared records are visible to the whole warp
+    if (BVH) {
+      bvh_trace(P, W, exact, lane);
+    } else {
+      uint32_t n_entries = 0xffffffffu;  // RT_FLAG_NO_FILTER: no list, every lane scans every sphere
+      if (!P.no_filter) n_entries = filter_rays<G, CROWS>(P, CR, W, glist, lane);
+      __syncwarp();
+      if (n_entries <= kListSmem + 64u * kListGlobalPerSlot) resolve_entries<G, F32HIT>(P, W, glist, n_entries, exact, lane);
+      else resolve_scan<F32HIT>(P, W, exact, lane);
+    }
+    __syncwarp();
   }
 }
 
 // ================================================================ host side
 size_t wave_pool_bytes(uint32_t n_slots) {
-  // ray_o, ray_d, thr, acc (float4) + it (uint4) + cand_cnt + cand_idx planes
-  return (size_t)n_slots * (5 * 16 + 4 + 4 * (size_t)kCandPlanes);
+  // thr, acc (float4) + it (uint4) + the candidate entries beyond the shared-memory lists
+  return (size_t)n_slots * (3 * 16 + 4 * (size_t)kListGlobalPerSlot);
 }
 
 uint32_t wave_default_slots(int sm_count) {
-  // a whole number of filter-kernel rounds: SMs x resident lanes x rays per lane x rounds
-  // (also the capacity the fused kernel needs at R = 4)
-  return (uint32_t)sm_count * RTW_MINB * kWBlock * 2u * 2u;
+  // SMs x resident CTAs (the BVH form takes one more) x lanes x 2 slots per lane
+  return (uint32_t)sm_count * (RTW_MINB + 1) * kWBlock * 2u;
 }
 
-void wave_carve(WaveParams &p, void *pool, uint32_t n_slots) {
+static void wave_carve(WaveParams &p, void *pool, uint32_t n_slots) {
   unsigned char *b = static_cast<unsigned char *>(pool);
   size_t n = n_slots;
   p.n_slots = n_slots;
-  p.ray_o = reinterpret_cast<float4 *>(b); b += n * 16;
-  p.ray_d = reinterpret_cast<float4 *>(b); b += n * 16;
   p.thr = reinterpret_cast<float4 *>(b); b += n * 16;
   p.acc = reinterpret_cast<float4 *>(b); b += n * 16;
   p.it = reinterpret_cast<uint4 *>(b); b += n * 16;
-  p.cand_cnt = reinterpret_cast<uint32_t *>(b); b += n * 4;
-  p.cand_idx = reinterpret_cast<uint32_t *>(b);
+  p.glist = reinterpret_cast<uint32_t *>(b);
 }
 
-template <int R, int G>
-static cudaError_t launch_filter_t(const WaveParams &p, const ConstRows &cr, bool crows, int grid,
-                                   cudaStream_t st) {
-  if (crows)
-    filter_kernel<R, G, true><<<grid, kWBlock, 0, st>>>(p, cr);
-  else
-    filter_kernel<R, G, false><<<grid, kWBlock, 0, st>>>(p, cr);
-  return cudaGetLastError();
-}
-
-cudaError_t run_wavefront(const WaveParams &p, const float4 *host_rows, int sm_count,
-                          size_t smem_optin_max, cudaStream_t st, unsigned int *host_live,
-                          WaveRunInfo *info) {
-  static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
-  const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
-                     !env_cfg().no_const_rows;
-  if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
-  const int rpl = env_cfg().rays_per_lane;
-  if (rpl != 2 && rpl != 4) return cudaErrorInvalidValue;
-  if (p.n_slots % (kWBlock * 4u)) return cudaErrorInvalidValue;
-
-  // shade kernel: per-hit rows in shared memory when they fit
-  const size_t scene_smem = (size_t)p.scene.n_pad * 56;
-  const bool in_smem = scene_smem + 1024 <= smem_optin_max / 4;
-  cudaError_t e;
-  if (in_smem) {
-    e = cudaFuncSetAttribute(shade_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scene_smem);
-    if (e != cudaSuccess) return e;
-  }
-  int shade_per_sm = 0;
-  e = in_smem ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&shade_per_sm, shade_kernel<true>, 256, scene_smem)
-              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&shade_per_sm, shade_kernel<false>, 256, 0);
-  if (e != cudaSuccess) return e;
-  if (shade_per_sm < 1) return cudaErrorLaunchOutOfResources;
-  const int shade_grid = sm_count * shade_per_sm;
-  const int filter_grid = sm_count * RTW_MINB;
-
-  auto shade = [&]() -> cudaError_t {
-    if (in_smem) shade_kernel<true><<<shade_grid, 256, scene_smem, st>>>(p);
-    else shade_kernel<false><<<shade_grid, 256, 0, st>>>(p);
-    return cudaGetLastError();
-  };
-  auto filter = [&]() -> cudaError_t {
-    return rpl == 4 ? launch_filter_t<4, RTW_G>(p, cr, crows, filter_grid, st)
-                    : launch_filter_t<2, RTW_G>(p, cr, crows, filter_grid, st);
-  };
-
-  uint32_t launches = 0, waves = 0;
-  wave_init_kernel<<<sm_count * 4, 256, 0, st>>>(p);
-  if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  ++launches;
-
-  // every sample needs at least one wave of its slot: no need to poll before that many waves
-  uint64_t total_samples = 0;
-  for (uint32_t k = p.slice_begin; k < p.slice_end; ++k) {
-    uint32_t a, b;
-    slice_range(k, p.spp, a, b);
-    total_samples += b - a;
-  }
-  total_samples *= (uint64_t)p.width * p.height;
-  const uint64_t min_waves = total_samples / p.n_slots;
-  const uint32_t poll_every = 4;
-
-  for (;;) {
-    const bool poll = waves >= min_waves && (waves - min_waves) % poll_every == 0;
-    if (poll && (e = cudaMemsetAsync(p.live, 0, sizeof(unsigned int), st)) != cudaSuccess) return e;
-    if ((e = shade()) != cudaSuccess) return e;
-    ++launches;
-    if (poll) {
-      if ((e = cudaMemcpyAsync(host_live, p.live, sizeof(unsigned int), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
-      if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
-      if (*host_live == 0) break;
-    }
-    if ((e = filter()) != cudaSuccess) return e;
-    ++launches;
-    ++waves;
-  }
-  if (info) {
-    info->launches = launches; info->waves = waves; info->n_slots = p.n_slots;
-    info->rays_per_lane = rpl; info->filter_grid = filter_grid; info->shade_grid = shade_grid;
-    info->rows_in_constant_bank = crows; info->scene_in_smem = in_smem;
-  }
-  return cudaSuccess;
-}
-
-template <int R, int G>
+template <int G>
 static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots, const ConstRows &cr,
                                   bool crows, bool in_smem, bool bvh, bool f32hit, size_t smem,
                                   int sm_count, int *grid_out, cudaStream_t st) {
 #define RTW_FUSED(CR_, SM_, BV_, ...)                                                              \
   do {                                                                                             \
-    auto k = fused_kernel<R, G, CR_, SM_, BV_, ##__VA_ARGS__>;                                     \
+    auto k = fused_kernel<G, CR_, SM_, BV_, ##__VA_ARGS__>;                                        \
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return e;                                                                \
     int per_sm = 0;                                                                                \
@@ -849,9 +761,9 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;                                          \
     /* persistent grid: every CTA must be resident (one full wave, a multiple of the SM count) */  \
     int want = BV_ ? kBvhMinB : RTW_MINB;                                                          \
-    while (want > 1 && (size_t)sm_count * want * kWBlock * R > pool_slots) --want;                 \
+    while (want > 1 && (size_t)sm_count * want * kWBlock * 2 > pool_slots) --want;                 \
     const int grid = sm_count * (per_sm < want ? per_sm : want);                                   \
-    const uint32_t n_slots = (uint32_t)grid * kWBlock * (uint32_t)R;                               \
+    const uint32_t n_slots = (uint32_t)grid * kWBlock * 2u;                                        \
     if (n_slots > pool_slots) return cudaErrorInvalidValue;                                        \
     wave_carve(p, pool, n_slots);                                                                  \
     *grid_out = grid;                                                                              \
@@ -875,22 +787,22 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
   if (use_bvh && !p.scene.bvh_nodes) return cudaErrorInvalidValue;
   if (use_bvh && f32_hit) return cudaErrorInvalidValue;
   static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
-  const bool crows = host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
+  const bool crows = !use_bvh && host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
                      !env_cfg().no_const_rows;
   if (crows) memcpy(cr.row, host_rows, (size_t)(p.scene.n_pad + kRowTail) * sizeof(float4));
-  const int rpl = env_cfg().rays_per_lane;
-  if (rpl != 2 && rpl != 4) return cudaErrorInvalidValue;
+  // shared memory of a CTA: the warps' states, then (when every resident CTA can afford it) the
+  // per-hit scene rows; an SM offers its opt-in maximum plus the 1 KB each CTA reserves
+  const size_t warp_smem = (size_t)kWarps * sizeof(WarpState);
   const size_t scene_smem = (size_t)p.scene.n_pad * 56;
-  const bool in_smem = (scene_smem + 1024) * RTW_MINB <= smem_optin_max;
-  const size_t smem = in_smem ? scene_smem : 0;
+  const size_t ctas = use_bvh ? kBvhMinB : RTW_MINB;
+  const bool in_smem = (warp_smem + scene_smem + 1024) * ctas <= smem_optin_max + 1024;
+  const size_t smem = warp_smem + (in_smem ? scene_smem : 0);
   int grid = 0;
-  cudaError_t e = rpl == 4 ? launch_fused_t<4, RTW_G>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st)
-                           : launch_fused_t<2, RTW_G>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem, sm_count, &grid, st);
-  const uint32_t n_slots = p.n_slots;
+  cudaError_t e = launch_fused_t<RTW_G>(p, pool, pool_slots, cr, crows, in_smem, use_bvh, f32_hit, smem,
+                                        sm_count, &grid, st);
   if (info) {
-    info->launches = 1; info->waves = 0; info->n_slots = n_slots; info->rays_per_lane = rpl;
-    info->filter_grid = grid; info->shade_grid = 0; info->rows_in_constant_bank = crows;
-    info->scene_in_smem = in_smem;
+    info->launches = 1; info->n_slots = p.n_slots; info->rays_per_lane = 2; info->grid = grid;
+    info->rows_in_constant_bank = crows; info->scene_in_smem = in_smem;
   }
   return e;
 }

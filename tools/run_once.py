@@ -4,6 +4,7 @@
     python tools/run_once.py --scene cover --w 1200 --h 675 --spp 64 [--reps 3] [--ppm out.ppm]
 """
 import argparse
+import hashlib
 import json
 import os
 import sys
@@ -63,7 +64,8 @@ def main():
             "render_ms": st.render_ms, "finalize_ms": fin.finalize_ms, "samples": st.samples,
             "rays": fin.rays, "msamples_s": st.samples / st.render_ms / 1e3,
             "mrays_s": fin.rays / st.render_ms / 1e3,
-            "tflops_algorithmic": tests * 17 / (st.render_ms * 1e-3) / 1e12}))
+            "tflops_algorithmic": tests * 17 / (st.render_ms * 1e-3) / 1e12,
+            "image_sha256": hashlib.sha256(rgb.tobytes()).hexdigest()[:16]}))
     if a.ppm:
         rt.write_ppm(a.ppm, rgb)
 
