@@ -7,9 +7,15 @@
 //                                  focal length 1  ==  (0,0,0)->(0,0,-1), vfov 90, aperture 0, focus 1
 //   camera(vfov, aspect)           archive/listing62/camera.h        same with vfov
 //   camera(from, at, vup, vfov, aspect)  archive/listing64/camera.h:8-25   aperture 0, focus 1
-// The kernels always apply the FINAL material rules of src/cpu/material.h (the archive's
-// material.h snapshots of earlier steps — e.g. the always-refracting glass of listing55 — are
-// not separate code paths); what is covered is the scene construction variants.
+// The material steps (listing50 on) run the FINAL material rules of src/cpu/material.h (the
+// archive's material.h snapshots of earlier steps — e.g. the always-refracting glass of
+// listing55 — are not separate code paths).  The diffuse-only steps before them (listing33-40:
+// no material classes yet, the rule is written inside ray_color) have their own rules in the
+// kernels, carried by book::diffuse: RT_DIFFUSE_BALL = normal + random_in_unit_sphere()
+// (listing33/main.cc:12-13), RT_LAMBERTIAN = normal + random_unit_vector() (listing38/main.cc:26),
+// RT_DIFFUSE_HEMI = random_in_hemisphere(normal) (listing40/main.cc:26); listing34's write_color
+// has no gamma yet (RT_FLAG_LINEAR_OUTPUT).  Not reproduced: the t_min = 0 of listing33/34
+// (shadow acne, fixed by the book in listing36) and listing33's missing bounce limit.
 #ifndef RT_BOOK_SCENES_HPP
 #define RT_BOOK_SCENES_HPP
 
@@ -30,6 +36,22 @@ struct step {
   int image_width;      // the listing's literals
   double aspect_ratio;
   int samples_per_pixel, max_depth;
+  uint32_t flags = 0;   // RT_FLAG_* the step needs (RT_FLAG_LINEAR_OUTPUT before listing35)
+};
+
+// The diffuse rule of a step that has no material classes yet: ray_color itself says
+// `0.5 * ray_color(ray(rec.p, target - rec.p), ...)` with one of three targets.
+class diffuse : public material {
+ public:
+  enum rule_t { in_unit_sphere, unit_vector, in_hemisphere };
+  rule_t rule;
+  double reflectance;
+  diffuse(rule_t r, double refl = 0.5) : rule(r), reflectance(refl) {}
+  void describe(rt_sphere &o) const override {
+    o.kind = rule == in_unit_sphere ? RT_DIFFUSE_BALL : rule == unit_vector ? RT_LAMBERTIAN : RT_DIFFUSE_HEMI;
+    o.albedo[0] = o.albedo[1] = o.albedo[2] = reflectance;
+    o.fuzz_or_ir = 0.0;
+  }
 };
 
 namespace detail {
@@ -52,6 +74,34 @@ inline hittable_list trio(shared_ptr<material> ground, shared_ptr<material> cent
   return world;
 }
 }  // namespace detail
+
+// The two-sphere world of the diffuse-only steps: archive/listing33/main.cc:34-36 (small sphere
+// first, then the ground), default camera, 400 px, 100 spp.
+inline step diffuse_step(const char *name, const char *listing, diffuse::rule_t rule, uint32_t flags) {
+  auto m = make_shared<diffuse>(rule);
+  hittable_list world;
+  world.add(make_shared<sphere>(point3(0, 0, -1), 0.5, m));
+  world.add(make_shared<sphere>(point3(0, -100.5, -1), 100, m));
+  step s{name, listing, world, detail::default_camera(), 400, detail::kAspect, 100, 50};
+  s.flags = flags;
+  return s;
+}
+// "First render of a diffuse sphere" with the bounce limit: archive/listing34/main.cc:9-24, linear output
+inline step diffuse_first() {
+  return diffuse_step("diffuse_first", "archive/listing34/main.cc:9-24", diffuse::in_unit_sphere, RT_FLAG_LINEAR_OUTPUT);
+}
+// gamma 2 (listing35/color.h) and t_min = 0.001: archive/listing36/main.cc:19-32
+inline step diffuse_gamma() {
+  return diffuse_step("diffuse_gamma", "archive/listing36/main.cc:19-32", diffuse::in_unit_sphere, 0);
+}
+// "True Lambertian": target = p + normal + random_unit_vector(), archive/listing38/main.cc:26
+inline step diffuse_lambertian() {
+  return diffuse_step("diffuse_lambertian", "archive/listing38/main.cc:26", diffuse::unit_vector, 0);
+}
+// hemispherical scattering: target = p + random_in_hemisphere(normal), archive/listing40/main.cc:26
+inline step diffuse_hemisphere() {
+  return diffuse_step("diffuse_hemisphere", "archive/listing40/main.cc:26", diffuse::in_hemisphere, 0);
+}
 
 // "Shiny metal": two mirror-like metals.  archive/listing50/main.cc:53-64 (metal(color) of that
 // step == fuzz 0 of the final class, src/cpu/material.h:38)
@@ -129,7 +179,7 @@ inline step final_cover() {
 }
 
 inline std::vector<step> all() {
-  return {shiny_metal(), fuzzed_metal(), glass_pair(), glass_single(), hollow_glass(), wide_angle(),
+  return {diffuse_first(), diffuse_gamma(), diffuse_lambertian(), diffuse_hemisphere(), shiny_metal(), fuzzed_metal(), glass_pair(), glass_single(), hollow_glass(), wide_angle(),
           distant_view(), zoomed_view(), defocus_blur(), final_cover()};
 }
 

@@ -209,13 +209,14 @@ inline void render(color *frame_buffer, const camera *cam, const hittable *world
 
 // output_image + write_color, src/gpu/camera.h:197-210 and color.h:17-38 (f32: scale, sqrt,
 // clamp to [0, 0.999], 256x), P3 text on stdout — through the library's table-driven writer
-inline void output_image(const camera *cam, const color *frame_buffer, const char *path = "-") {
+// (gamma = false: the colour write of archive-gpu/image7...11, before linear_to_gamma)
+inline void output_image(const camera *cam, const color *frame_buffer, const char *path = "-", bool gamma = true) {
   const size_t npix = (size_t)cam->image_width * cam->image_height;
   std::vector<uint8_t> rgb(npix * 3);
   const float scale = 1.0f / cam->samples_per_pixel;
   for (size_t p = 0; p < npix; ++p)
     for (int k = 0; k < 3; ++k) {
-      float x = std::sqrt((float)frame_buffer[p][k] * scale);
+      float x = gamma ? std::sqrt((float)frame_buffer[p][k] * scale) : (float)frame_buffer[p][k] * scale;
       x = x < 0.000f ? 0.000f : (0.999f < x ? 0.999f : x);
       rgb[p * 3 + k] = (uint8_t)static_cast<int>(256.0f * x);
     }

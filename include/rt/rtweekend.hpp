@@ -283,7 +283,7 @@ struct image {
 // The pixel/sample loops of main() (src/cpu/main.cc:111-123) as one call.
 inline image render(const hittable_list &world, const camera &cam, uint32_t image_width,
                     uint32_t image_height, uint32_t samples_per_pixel, uint32_t max_depth,
-                    uint64_t seed = 0, int device = 0, bool use_bvh = false) {
+                    uint64_t seed = 0, int device = 0, bool use_bvh = false, uint32_t flags = 0) {
   std::vector<rt_sphere> flat = world.flatten();
   rt_scene *sc = nullptr;
   check(rt_scene_create(flat.data(), (uint32_t)flat.size(), device, &sc));
@@ -291,7 +291,7 @@ inline image render(const hittable_list &world, const camera &cam, uint32_t imag
   cfg.width = image_width; cfg.height = image_height;
   cfg.samples_per_pixel = samples_per_pixel; cfg.max_depth = max_depth;
   cfg.seed = seed; cfg.slice_begin = 0; cfg.slice_end = RT_SLICES; cfg.device = device;
-  cfg.flags = use_bvh ? RT_FLAG_BVH : 0u;
+  cfg.flags = (use_bvh ? RT_FLAG_BVH : 0u) | flags;
   image img;
   img.width = image_width; img.height = image_height;
   img.rgb.resize((size_t)image_width * image_height * 3);

@@ -30,7 +30,10 @@ extern "C" {
 #define RT_LAMBERTIAN 0u /* src/cpu/material.h:14-34 */
 #define RT_METAL 1u      /* src/cpu/material.h:36-51 */
 #define RT_DIELECTRIC 2u /* src/cpu/material.h:53-87 */
-#define RT_KIND_MAX RT_DIELECTRIC
+/* the diffuse rules of the book's earlier steps (no material classes yet; albedo = the 0.5 of the listing) */
+#define RT_DIFFUSE_BALL 3u /* direction = normal + random_in_unit_sphere(), archive/listing33/main.cc:12-13 */
+#define RT_DIFFUSE_HEMI 4u /* direction = random_in_hemisphere(normal), archive/listing40/main.cc:26 */
+#define RT_KIND_MAX RT_DIFFUSE_HEMI
 
 #define RT_SLICES 64u /* canonical sample slices per pixel (multi-GPU split) */
 
@@ -84,7 +87,11 @@ typedef struct rt_config {
                                  written, src/cpu/hittable_list.h:28-43).  The image must be byte-identical with
                                  and without it: that is the test of the filter's conservativeness
                                  (tests/test_filter_soundness.py).  ~50x slower; brute-force scan only. */
-#define RT_FLAG_ALL (RT_FLAG_COUNT_RAYS | RT_FLAG_BVH | RT_FLAG_V4_MODEL | RT_FLAG_F32_HIT | RT_FLAG_NO_FILTER)
+#define RT_FLAG_LINEAR_OUTPUT 128u /* rt_finalize quantises sum/spp without the gamma sqrt: the write_color of the
+                                 book's first diffuse steps (archive/listing30/color.h:8-17, before listing35;
+                                 archive-gpu/image7...11/color.h) */
+#define RT_FLAG_ALL (RT_FLAG_COUNT_RAYS | RT_FLAG_BVH | RT_FLAG_V4_MODEL | RT_FLAG_F32_HIT | RT_FLAG_NO_FILTER | \
+                     RT_FLAG_LINEAR_OUTPUT)
 
 typedef struct rt_stats {
   uint64_t samples;      /* samples traced by this call */

@@ -377,6 +377,20 @@ static int scatter(const double *s, v3 dir_in, const hitrec *rec, rng_t *g, v3 *
     *atten = V(s[5], s[6], s[7]);
     return 1;
   }
+  if (kind == ORC_DIFFUSE_BALL || kind == ORC_DIFFUSE_HEMI) {
+    /* archive/listing33/main.cc:12-13 (listing36: t_min 0.001) and archive/listing40/main.cc:26 with
+     * random_in_hemisphere of archive/listing39/vec3.h:110-116; the 0.5 of those listings is the
+     * row's albedo */
+    v3 ball = g->mode == ORC_RNG_MT19937 ? mt_in_unit_sphere(g->c)
+                                         : direct_in_unit_sphere(xi[0], xi[1], xi[2]);
+    if (kind == ORC_DIFFUSE_BALL) {
+      *dir_out = vadd(rec->normal, ball);
+    } else {
+      *dir_out = vdot(ball, rec->normal) > 0.0 ? ball : vneg(ball);
+    }
+    *atten = V(s[5], s[6], s[7]);
+    return 1;
+  }
   if (kind == ORC_METAL) {
     v3 reflected = vreflect(vunit(dir_in), rec->normal);
     v3 ball = g->mode == ORC_RNG_MT19937 ? mt_in_unit_sphere(g->c)

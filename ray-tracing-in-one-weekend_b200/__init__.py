@@ -18,12 +18,14 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
+DIFFUSE_BALL, DIFFUSE_HEMI = 3, 4  # the book's earlier diffuse rules (archive/listing33, listing40)
 SLICES = 64
 FLAG_COUNT_RAYS = 1
 FLAG_BVH = 8
 FLAG_V4_MODEL = 16  # src/gpu (v4 book) semantics, see include/rt_b200.h
 FLAG_F32_HIT = 32   # f32 sphere::hit like src/gpu/sphere.h (compatibility/diagnostic)
 FLAG_NO_FILTER = 64  # soundness switch: no f32 pre-test, every ray resolves every sphere in f64
+FLAG_LINEAR_OUTPUT = 128  # write_color without the gamma sqrt (the book's first diffuse steps)
 PNM_P3, PNM_P6 = 3, 6
 
 

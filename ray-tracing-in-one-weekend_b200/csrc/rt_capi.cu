@@ -529,7 +529,8 @@ int rt_finalize_enqueue(rt_frame *f, const rt_config *cfg, const void *const *pa
   CU(cudaMemsetAsync(f->counters + 1, 0, sizeof(unsigned long long), f->stream));
   CU(cudaEventRecord(f->ev[2], f->stream));
   float scale = 1.0f / (float)cfg->samples_per_pixel;
-  CU(launch_finalize(ptrs, count, f->npix, scale, f->rgb_words, linear_out ? f->linear : nullptr,
+  CU(launch_finalize(ptrs, count, f->npix, scale, !(cfg->flags & RT_FLAG_LINEAR_OUTPUT), f->rgb_words,
+                     linear_out ? f->linear : nullptr,
                      f->counters + 1, f->sm_count, f->stream));
   CU(cudaEventRecord(f->ev[3], f->stream));
   if (rgb8_out)

@@ -59,9 +59,11 @@ __global__ void __launch_bounds__(256) reduce_local_kernel(const float4 *__restr
     dst[i] = tree_sum_planes<N>(first_plane, npix, i);
 }
 
-// write_color, src/cpu/color.h:8-23: x = sqrt(sum/spp); int(256 * clamp(x, 0, 0.999)).
-__device__ __forceinline__ uint32_t quantise(float sum, float scale) {
-  float x = sqrtf(scale * sum);
+// write_color, src/cpu/color.h:8-23: x = sqrt(sum/spp); int(256 * clamp(x, 0, 0.999)).  gamma =
+// false is the write_color of the book's first diffuse steps (no sqrt yet: archive/listing30/color.h,
+// archive-gpu/image7...11/color.h), RT_FLAG_LINEAR_OUTPUT.
+__device__ __forceinline__ uint32_t quantise(float sum, float scale, bool gamma) {
+  float x = gamma ? sqrtf(scale * sum) : scale * sum;
   x = fminf(fmaxf(x, 0.0f), 0.999f);
   return (uint32_t)(int)(256.0f * x);
 }
@@ -70,7 +72,7 @@ __device__ __forceinline__ uint32_t quantise(float sum, float scale) {
 // warp writes 384 contiguous bytes).  Ray counts (w channel) are block-reduced to one atomic.
 template <int N>
 __global__ void __launch_bounds__(256) finalize_kernel(const __grid_constant__ PtrPack src,
-                                                       uint32_t npix, float scale,
+                                                       uint32_t npix, float scale, bool gamma,
                                                        uint32_t *__restrict__ rgb_words,
                                                        float *__restrict__ linear,
                                                        unsigned long long *__restrict__ rays) {
@@ -91,9 +93,9 @@ __global__ void __launch_bounds__(256) finalize_kernel(const __grid_constant__ P
         }
       }
       my_rays += (double)v.w;
-      c[k * 3 + 0] = quantise(v.x, scale);
-      c[k * 3 + 1] = quantise(v.y, scale);
-      c[k * 3 + 2] = quantise(v.z, scale);
+      c[k * 3 + 0] = quantise(v.x, scale, gamma);
+      c[k * 3 + 1] = quantise(v.y, scale, gamma);
+      c[k * 3 + 2] = quantise(v.z, scale, gamma);
     }
     // rgb_words is padded to a multiple of 12 bytes by the host
     rgb_words[qd * 3 + 0] = c[0] | (c[1] << 8) | (c[2] << 16) | (c[3] << 24);
@@ -273,16 +275,16 @@ cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t sli
 }
 
 cudaError_t launch_finalize(const float4 *const *partials, uint32_t count, uint32_t npix,
-                            float scale, uint32_t *rgb_words, float *linear,
+                            float scale, bool gamma, uint32_t *rgb_words, float *linear,
                             unsigned long long *rays, int sm_count, cudaStream_t st) {
   PtrPack pk{};
   for (uint32_t k = 0; k < count && k < 8; ++k) pk.p[k] = partials[k];
   int grid = grid_for((npix + 3) / 4, sm_count);
   switch (count) {
-    case 1: finalize_kernel<1><<<grid, 256, 0, st>>>(pk, npix, scale, rgb_words, linear, rays); break;
-    case 2: finalize_kernel<2><<<grid, 256, 0, st>>>(pk, npix, scale, rgb_words, linear, rays); break;
-    case 4: finalize_kernel<4><<<grid, 256, 0, st>>>(pk, npix, scale, rgb_words, linear, rays); break;
-    case 8: finalize_kernel<8><<<grid, 256, 0, st>>>(pk, npix, scale, rgb_words, linear, rays); break;
+    case 1: finalize_kernel<1><<<grid, 256, 0, st>>>(pk, npix, scale, gamma, rgb_words, linear, rays); break;
+    case 2: finalize_kernel<2><<<grid, 256, 0, st>>>(pk, npix, scale, gamma, rgb_words, linear, rays); break;
+    case 4: finalize_kernel<4><<<grid, 256, 0, st>>>(pk, npix, scale, gamma, rgb_words, linear, rays); break;
+    case 8: finalize_kernel<8><<<grid, 256, 0, st>>>(pk, npix, scale, gamma, rgb_words, linear, rays); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();

@@ -111,7 +111,7 @@ cudaError_t launch_reduce_local(const float4 *accum, uint32_t npix, uint32_t sli
 
 // partials: `count` device pointers (count in {1,2,4,8}) in rank order.
 cudaError_t launch_finalize(const float4 *const *partials, uint32_t count, uint32_t npix,
-                            float scale, uint32_t *rgb_words, float *linear,
+                            float scale, bool gamma, uint32_t *rgb_words, float *linear,
                             unsigned long long *rays, int sm_count, cudaStream_t st);
 
 cudaError_t launch_primary_f32(const SceneView &sc, const CameraF32 &cam, uint32_t W, uint32_t H,

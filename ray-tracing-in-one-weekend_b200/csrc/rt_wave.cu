@@ -483,6 +483,18 @@ __device__ __forceinline__ uint32_t shade_slot(const WaveParams &P, WarpState &W
         if (kind == 0u) {
           sx = nx + ux; sy = ny + uy; sz = nz + uz;
           if (fabsf(sx) < 1e-8f && fabsf(sy) < 1e-8f && fabsf(sz) < 1e-8f) { sx = nx; sy = ny; sz = nz; }
+        } else if (kind >= 3u) {
+          // the book's earlier diffuse rules: a point INSIDE the unit ball, added to the normal
+          // (archive/listing33/main.cc:12-13) or flipped into the normal's hemisphere
+          // (archive/listing40/main.cc:26, random_in_hemisphere of listing39/vec3.h:110-116)
+          const float k = cbrtf(xi.z);
+          ux *= k; uy *= k; uz *= k;
+          if (kind == 3u) {
+            sx = nx + ux; sy = ny + uy; sz = nz + uz;
+          } else {
+            const bool same = (ux * nx + uy * ny + uz * nz) > 0.0f;
+            sx = same ? ux : -ux; sy = same ? uy : -uy; sz = same ? uz : -uz;
+          }
         } else {
           sx = dx - 2.0f * dn * nx; sy = dy - 2.0f * dn * ny; sz = dz - 2.0f * dn * nz;
           if (M.w > 0.0f) {
