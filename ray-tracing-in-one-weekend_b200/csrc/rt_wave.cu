@@ -110,13 +110,19 @@ __device__ __forceinline__ uint32_t filter_rays(const WaveParams &P, const Const
       const uint32_t g = s0 / (uint32_t)G;
       const uint32_t n0 = __popc(b0);
       const uint32_t pos0 = wcnt + __popc(b0 & lt), pos1 = wcnt + n0 + __popc(b1 & lt);
-      if (p0) {
-        if (pos0 < kListSmem) W.list[pos0] = e0 | g;
-        else if (pos0 - kListSmem < gcap) glist[pos0 - kListSmem] = e0 | g;
-      }
-      if (p1) {
-        if (pos1 < kListSmem) W.list[pos1] = e1 | g;
-        else if (pos1 - kListSmem < gcap) glist[pos1 - kListSmem] = e1 | g;
+      if (wcnt <= kListSmem - 64u) {
+        // the 64 entries a group can add fit the shared-memory list: no capacity checks
+        if (p0) W.list[pos0] = e0 | g;
+        if (p1) W.list[pos1] = e1 | g;
+      } else {
+        if (p0) {
+          if (pos0 < kListSmem) W.list[pos0] = e0 | g;
+          else if (pos0 - kListSmem < gcap) glist[pos0 - kListSmem] = e0 | g;
+        }
+        if (p1) {
+          if (pos1 < kListSmem) W.list[pos1] = e1 | g;
+          else if (pos1 - kListSmem < gcap) glist[pos1 - kListSmem] = e1 | g;
+        }
       }
       wcnt += n0 + __popc(b1);
       // @phase main-loop
