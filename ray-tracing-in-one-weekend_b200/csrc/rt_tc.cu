@@ -1,0 +1,323 @@
+// csrc/rt_tc.cu — the line-sphere filter as ONE contraction on the 5th-generation tensor cores
+// (tcgen05, sm_100a): probe kernel + host-side operand builder.
+//
+// The brute-force filter of rt_wave.cu decides, per (ray, sphere), the sign of
+//     e = (c.d - o.d)^2 + 2 c.o + (r^2 - |c|^2) - |o|^2            (>= 0: the line meets the sphere)
+// Expanded, e is a dot product of 11 SPHERE features with 11 RAY features,
+//     phi(c, r) = [cx^2, cy^2, cz^2, cx cy, cx cz, cy cz, cx, cy, cz, w, 1]
+//     psi(o, d) = [dx^2, dy^2, dz^2, 2 dx dy, 2 dx dz, 2 dy dz, q_x, q_y, q_z, 1, k]
+//     q = 2 (o - (o.d) d),   k = (o.d)^2 - |o|^2,   w = r^2 - |c|^2,
+// i.e. a [rays x K] x [K x spheres] matrix product: hittable_list::hit's "every ray against every
+// sphere" (src/cpu/hittable_list.h:28-43) is a dense contraction once it is written this way.
+// TF32 keeps 11 significant bits, so every feature is split x = hi + lo and the three products
+// hi*hi + lo*hi + hi*lo take three K slots (the 3xTF32 scheme): 9 x 3 + 2 + 2 = 31 -> K = 32, four
+// tcgen05.mma.kind::tf32 steps of K = 8 with fp32 accumulation in tensor memory.
+//
+//   rays    = the M operand (128 rows = the 128 TMEM lanes = 128 threads: thread <-> ray), written
+//             by the threads themselves with tcgen05.st (A operand read from TMEM);
+//   spheres = the N operand, K-major, no swizzle, resident in shared memory for the whole kernel;
+//   D       = [128 rays x 64 spheres] fp32 in TMEM; each thread reads ITS ray's row with
+//             tcgen05.ld and folds the 64 sign bits into a mask: no FMA left in the epilogue.
+//
+// Conservativeness: the split, the fp32 feature arithmetic and the accumulation perturb e by at
+// most kappa * (A_s + B_r), A_s = 2|c|^2 + |w|, B_r = 2|o|^2 (bound of sum |phi_i psi_i|); kappa A_s
+// is folded into w on the host, kappa B_r into k on the device, like the SIMT filter's slack.
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "rt_capi_internal.h"
+
+namespace rtb {
+
+constexpr int kTcK = 32;          // K slots (4 MMA steps of 8)
+constexpr int kTcTile = 64;       // spheres per MMA (N)
+constexpr float kTcKappa = 1.52587890625e-05f;  // 2^-16
+
+// ---------------------------------------------------------------- host: sphere operand
+static float tf32_trunc(float x) {
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  u &= 0xffffe000u;  // 1 + 8 + 10 bits
+  memcpy(&x, &u, 4);
+  return x;
+}
+static void split_tf32(double x, float &hi, float &lo) {
+  hi = tf32_trunc((float)x);
+  lo = tf32_trunc((float)(x - (double)hi));
+}
+
+// Canonical K-major, no-swizzle layout of one [64 spheres x 8 K] slab (2048 B): core matrices of
+// 8 rows x 16 B; the two K halves of a row group 128 B apart (LBO), row groups 256 B apart (SBO).
+static size_t slab_offset(int row, int k) {
+  return (size_t)(row / 8) * 256 + (size_t)(k / 4) * 128 + (size_t)(row % 8) * 16 + (size_t)(k % 4) * 4;
+}
+
+// spheres {cx, cy, cz, signed r} -> [tiles][4 K steps][2048 B]; padding rows can never pass (w = -big)
+void tc_build_sphere_operand(const double4 *exact, uint32_t n, std::vector<float> &out, uint32_t &tiles) {
+  tiles = (n + kTcTile - 1) / kTcTile;
+  if (tiles == 0) tiles = 1;
+  out.assign((size_t)tiles * 4 * 512, 0.0f);
+  for (uint32_t s = 0; s < tiles * kTcTile; ++s) {
+    double f[11];
+    if (s < n) {
+      const double cx = exact[s].x, cy = exact[s].y, cz = exact[s].z, r = exact[s].w;
+      const double c2 = cx * cx + cy * cy + cz * cz, w = r * r - c2;
+      f[0] = cx * cx; f[1] = cy * cy; f[2] = cz * cz; f[3] = cx * cy; f[4] = cx * cz; f[5] = cy * cz;
+      f[6] = cx; f[7] = cy; f[8] = cz;
+      f[9] = w + (double)kTcKappa * (2.0 * c2 + std::fabs(w));  // slack: can only ADD candidates
+      f[10] = 1.0;
+    } else {
+      for (int k = 0; k < 11; ++k) f[k] = 0.0;
+      f[9] = -1.0e30;
+    }
+    float slot[kTcK];
+    for (int k = 0; k < kTcK; ++k) slot[k] = 0.0f;
+    for (int i = 0; i < 9; ++i) {  // psi side holds [hi, lo, hi]
+      float hi, lo;
+      split_tf32(f[i], hi, lo);
+      slot[3 * i] = hi; slot[3 * i + 1] = hi; slot[3 * i + 2] = lo;
+    }
+    slot[27] = 1.0f; slot[28] = 1.0f;  // x the ray's constant k (hi, lo)
+    {
+      // the truncating split loses at most 2^-20 |w|: add it first, so that the slack only grows
+      float hi, lo;
+      split_tf32(f[9] + std::fabs(f[9]) * 0x1p-19, hi, lo);
+      slot[29] = hi; slot[30] = lo;    // x 1, 1
+    }
+    const uint32_t tile = s / kTcTile, row = s % kTcTile;
+    for (int k = 0; k < kTcK; ++k) {
+      const size_t off = ((size_t)tile * 4 + k / 8) * 2048 + slab_offset((int)row, k % 8);
+      out[off / 4] = slot[k];
+    }
+  }
+}
+
+// ---------------------------------------------------------------- device helpers (tcgen05)
+__device__ __forceinline__ float d_tf32_trunc(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t *slot_in_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(slot_in_smem)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[tmem] x B[smem descriptor], kind::tf32, one CTA
+__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+// shared-memory matrix descriptor: K-major, no swizzle, LBO = 128 B, SBO = 256 B, version 1 (Blackwell)
+__device__ __forceinline__ uint64_t tc_smem_desc(const void *p) {
+  const uint64_t a = (uint64_t)((smem_addr(p) >> 4) & 0x3fffu);
+  return a | (8ull << 16) | (16ull << 32) | (1ull << 46);
+}
+// instruction descriptor: D = f32, A = B = tf32, both K-major, M = 128, N = 64
+constexpr uint32_t kTcIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTcTile >> 3) << 17) | ((128u >> 4) << 24);
+
+// bounded wait: a wrong descriptor must not hang the GPU box
+__device__ __forceinline__ bool mbar_wait_bounded(uint64_t *bar, uint32_t parity) {
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(ok)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+    if (ok) return true;
+    if (clock64() - t0 > 200000000ll) return false;  // ~0.1 s
+  }
+}
+
+// psi(o, d) -> the ray's 32 K slots {hi, lo, hi} x 9, k (hi, lo), 1, 1, 0
+__device__ __forceinline__ void tc_ray_slots(const float4 o, const float4 d, uint32_t (&slot)[kTcK]) {
+  const float od = o.x * d.x + o.y * d.y + o.z * d.z;
+  const float o2 = o.x * o.x + o.y * o.y + o.z * o.z;
+  float f[9] = {d.x * d.x, d.y * d.y, d.z * d.z, 2.0f * d.x * d.y, 2.0f * d.x * d.z, 2.0f * d.y * d.z,
+                2.0f * (o.x - od * d.x), 2.0f * (o.y - od * d.y), 2.0f * (o.z - od * d.z)};
+#pragma unroll
+  for (int i = 0; i < 9; ++i) {
+    const float hi = d_tf32_trunc(f[i]), lo = d_tf32_trunc(f[i] - hi);
+    slot[3 * i] = __float_as_uint(hi); slot[3 * i + 1] = __float_as_uint(lo); slot[3 * i + 2] = __float_as_uint(hi);
+  }
+  // k = (o.d)^2 - |o|^2 + kappa * 2 |o|^2, plus a few ulps of |o|^2 for the f32 arithmetic above and
+  // 2^-19 |k| for the truncating split below: the slack can only ADD candidates.  A slot without a
+  // ray (o.w <= 0) gets k = -huge: it passes nothing.
+  float k = fmaf(od, od, -o2) + (2.0f * kTcKappa + 4.0e-7f) * o2;
+  k += fabsf(k) * 0x1p-19f;
+  if (!(o.w > 0.0f)) k = -1.0e30f;
+  const float kh = d_tf32_trunc(k), kl = d_tf32_trunc(k - kh);
+  slot[27] = __float_as_uint(kh); slot[28] = __float_as_uint(kl);
+  slot[29] = __float_as_uint(1.0f); slot[30] = __float_as_uint(1.0f);
+  slot[31] = 0u;
+}
+
+#define TC_ST32(addr, s)                                                                                   \
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, "   \
+               "%11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, " \
+               "%29, %30, %31, %32};" ::"r"(addr),                                                         \
+               "r"(s[0]), "r"(s[1]), "r"(s[2]), "r"(s[3]), "r"(s[4]), "r"(s[5]), "r"(s[6]), "r"(s[7]),      \
+               "r"(s[8]), "r"(s[9]), "r"(s[10]), "r"(s[11]), "r"(s[12]), "r"(s[13]), "r"(s[14]),            \
+               "r"(s[15]), "r"(s[16]), "r"(s[17]), "r"(s[18]), "r"(s[19]), "r"(s[20]), "r"(s[21]),          \
+               "r"(s[22]), "r"(s[23]), "r"(s[24]), "r"(s[25]), "r"(s[26]), "r"(s[27]), "r"(s[28]),          \
+               "r"(s[29]), "r"(s[30]), "r"(s[31])                                                          \
+               : "memory")
+
+#define TC_LD32(addr, v, o)                                                                                 \
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, " \
+               "%12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, "  \
+               "%30, %31}, [%32];"                                                                          \
+               : "=r"(v[o + 0]), "=r"(v[o + 1]), "=r"(v[o + 2]), "=r"(v[o + 3]), "=r"(v[o + 4]),            \
+                 "=r"(v[o + 5]), "=r"(v[o + 6]), "=r"(v[o + 7]), "=r"(v[o + 8]), "=r"(v[o + 9]),            \
+                 "=r"(v[o + 10]), "=r"(v[o + 11]), "=r"(v[o + 12]), "=r"(v[o + 13]), "=r"(v[o + 14]),       \
+                 "=r"(v[o + 15]), "=r"(v[o + 16]), "=r"(v[o + 17]), "=r"(v[o + 18]), "=r"(v[o + 19]),       \
+                 "=r"(v[o + 20]), "=r"(v[o + 21]), "=r"(v[o + 22]), "=r"(v[o + 23]), "=r"(v[o + 24]),       \
+                 "=r"(v[o + 25]), "=r"(v[o + 26]), "=r"(v[o + 27]), "=r"(v[o + 28]), "=r"(v[o + 29]),       \
+                 "=r"(v[o + 30]), "=r"(v[o + 31])                                                           \
+               : "r"(addr)                                                                                  \
+               : "memory")
+
+// ---------------------------------------------------------------- probe kernel
+// One warpgroup (128 threads = 128 rays per block of rays) per CTA, one CTA per SM.  For every
+// block of 128 rays: features -> TMEM, then per tile of 64 spheres 4 MMA steps, read back, fold
+// the sign bits into masks[ray][tile] (bit b set: sphere tile * 64 + b passes).  `values`
+// (optional) receives the raw e of the first `n_values` rays for the error measurement.
+__global__ void __launch_bounds__(128, 1)
+tc_filter_probe_kernel(const float4 *__restrict__ ray_o, const float4 *__restrict__ ray_d, uint32_t n_rays,
+                       const float *__restrict__ sphere_op, uint32_t tiles, unsigned long long *__restrict__ masks,
+                       float *__restrict__ values, uint32_t n_values, uint32_t repeats, unsigned int *__restrict__ status) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ uint32_t s_tmem;
+  float *s_op = reinterpret_cast<float *>(smem_raw);
+  const uint32_t tid = threadIdx.x, warp = tid >> 5;
+  for (uint32_t i = tid; i < tiles * 4u * 512u; i += 128u) s_op[i] = sphere_op[i];
+  if (tid == 0) mbar_init(&s_bar, 1);
+  if (warp == 0) tmem_alloc(&s_tmem, 128);
+  // generic-proxy writes of the operand must be visible to the tensor core's async proxy
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t lane_base = (warp * 32u) << 16;
+  const uint32_t a_tmem = tmem, d_tmem = tmem + 32u;
+  uint32_t parity = 0;
+  bool ok = true;
+  const uint32_t n_blocks = (n_rays + 127u) / 128u;
+  for (uint32_t rep = 0; rep < repeats; ++rep)
+    for (uint32_t blk = blockIdx.x; blk < n_blocks && ok; blk += gridDim.x) {
+      const uint32_t ray = blk * 128u + tid;
+      float4 o = make_float4(0.f, 0.f, 0.f, -1.f), d = make_float4(0.f, 1.f, 0.f, 0.f);
+      if (ray < n_rays) { o = ray_o[ray]; d = ray_d[ray]; }
+      uint32_t slot[kTcK];
+      tc_ray_slots(o, d, slot);
+      TC_ST32(a_tmem + lane_base, slot);
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncthreads();
+      for (uint32_t t = 0; t < tiles && ok; ++t) {
+        if (tid == 0) {
+          tc_fence_after();
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j)
+            tc_mma_ts(d_tmem, a_tmem + j * 8u, tc_smem_desc(s_op + ((size_t)t * 4 + j) * 512), kTcIdesc, j);
+          tc_commit(&s_bar);
+        }
+        ok = mbar_wait_bounded(&s_bar, parity);
+        parity ^= 1u;
+        tc_fence_after();
+        uint32_t v[kTcTile];
+        TC_LD32(d_tmem + lane_base, v, 0);
+        TC_LD32(d_tmem + lane_base + 32u, v, 32);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        tc_fence_before();
+        __syncthreads();  // D is free: the next tile's MMAs may overwrite it while the masks are built
+        uint32_t m0 = 0, m1 = 0;
+#pragma unroll
+        for (int b = 31; b >= 0; --b) { m0 = __funnelshift_l(v[b], m0, 1); m1 = __funnelshift_l(v[32 + b], m1, 1); }
+        // m has the SIGN bits: bit b = 1 -> e < 0 -> miss
+        const unsigned long long pass = ~((unsigned long long)m1 << 32 | m0);
+        if (ray < n_rays && rep == 0) {
+          masks[(size_t)ray * tiles + t] = pass;
+          if (values && ray < n_values)
+            for (int b = 0; b < kTcTile; ++b) values[((size_t)ray * tiles + t) * kTcTile + b] = __uint_as_float(v[b]);
+        }
+      }
+    }
+  if (!ok && tid == 0) atomicExch(status, 1u);
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+}  // namespace rtb
+
+using namespace rtb;
+
+// Measurement / validation aid: the tensor-core form of the filter on `n` rays
+// {o.xyz, |d| > 0} / {unit d} against the scene.  masks: HOST [n][tiles] 64-bit pass masks;
+// values: optional HOST [n_values][tiles][64] raw e; ms: device time of `repeats` passes over the rays.
+extern "C" int rt_tc_filter_probe(const rt_scene *sc, const float *ray_o, const float *ray_d, uint32_t n,
+                                  uint64_t *masks, uint32_t *tiles_out, float *values, uint32_t n_values,
+                                  uint32_t repeats, float *ms) {
+  if (!sc || !ray_o || !ray_d || !masks || !tiles_out) return rt_fail(RT_E_INVALID, "NULL argument");
+  if (sc->n == 0 || sc->n > 1024u) return rt_fail(RT_E_INVALID, "the probe keeps the sphere operand in shared memory: 1..1024 spheres");
+  CU(cudaSetDevice(sc->device));
+  const double4 *e = reinterpret_cast<const double4 *>(sc->stage);  // exact rows sit first in the staging buffer
+  std::vector<float> op;
+  uint32_t tiles = 0;
+  tc_build_sphere_operand(e, sc->n, op, tiles);
+  *tiles_out = tiles;
+  float4 *d_o = nullptr, *d_d = nullptr;
+  float *d_op = nullptr, *d_val = nullptr;
+  unsigned long long *d_m = nullptr;
+  unsigned int *d_st = nullptr, h_st = 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  const size_t op_bytes = op.size() * sizeof(float);
+  cudaError_t ce = cudaMalloc(&d_o, (size_t)n * 16);
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_d, (size_t)n * 16);
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_op, op_bytes);
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_m, (size_t)n * tiles * 8);
+  if (ce == cudaSuccess) ce = cudaMalloc(&d_st, 4);
+  if (ce == cudaSuccess && values && n_values) ce = cudaMalloc(&d_val, (size_t)n_values * tiles * kTcTile * 4);
+  if (ce == cudaSuccess) ce = cudaMemcpy(d_o, ray_o, (size_t)n * 16, cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaMemcpy(d_d, ray_d, (size_t)n * 16, cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaMemcpy(d_op, op.data(), op_bytes, cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) ce = cudaMemset(d_st, 0, 4);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&e0);
+  if (ce == cudaSuccess) ce = cudaEventCreate(&e1);
+  int sms = 0;
+  if (ce == cudaSuccess) ce = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, sc->device);
+  if (ce == cudaSuccess) ce = cudaFuncSetAttribute(tc_filter_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)op_bytes);
+  if (ce == cudaSuccess) {
+    const uint32_t blocks = (n + 127u) / 128u;
+    const int grid = (int)(blocks < (uint32_t)sms ? blocks : (uint32_t)sms);
+    cudaEventRecord(e0, 0);
+    tc_filter_probe_kernel<<<grid, 128, op_bytes>>>(d_o, d_d, n, d_op, tiles, d_m, d_val, d_val ? n_values : 0u,
+                                                    repeats ? repeats : 1u, d_st);
+    cudaEventRecord(e1, 0);
+    ce = cudaGetLastError();
+  }
+  if (ce == cudaSuccess) ce = cudaEventSynchronize(e1);
+  if (ce == cudaSuccess && ms) ce = cudaEventElapsedTime(ms, e0, e1);
+  if (ce == cudaSuccess) ce = cudaMemcpy(masks, d_m, (size_t)n * tiles * 8, cudaMemcpyDeviceToHost);
+  if (ce == cudaSuccess && d_val) ce = cudaMemcpy(values, d_val, (size_t)n_values * tiles * kTcTile * 4, cudaMemcpyDeviceToHost);
+  if (ce == cudaSuccess) ce = cudaMemcpy(&h_st, d_st, 4, cudaMemcpyDeviceToHost);
+  cudaFree(d_o); cudaFree(d_d); cudaFree(d_op); cudaFree(d_m); cudaFree(d_st); cudaFree(d_val);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  if (ce != cudaSuccess) return rt_fail(RT_E_CUDA, "tensor-core filter probe failed: %s", cudaGetErrorString(ce));
+  if (h_st) return rt_fail(RT_E_CUDA, "tensor-core filter probe: an MMA never completed (timeout)");
+  return RT_OK;
+}
