@@ -26,6 +26,7 @@ FLAG_V4_MODEL = 16  # src/gpu (v4 book) semantics, see include/rt_b200.h
 FLAG_F32_HIT = 32   # f32 sphere::hit like src/gpu/sphere.h (compatibility/diagnostic)
 FLAG_NO_FILTER = 64  # soundness switch: no f32 pre-test, every ray resolves every sphere in f64
 FLAG_LINEAR_OUTPUT = 128  # write_color without the gamma sqrt (the book's first diffuse steps)
+FLAG_SIMT_FILTER = 256  # FFMA2 filter loop instead of the tensor-core contraction (same image)
 PNM_P3, PNM_P6 = 3, 6
 
 

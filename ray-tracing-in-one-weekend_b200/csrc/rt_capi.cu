@@ -42,6 +42,7 @@ const EnvCfg &env_cfg() {
   static const EnvCfg cfg = [] {
     EnvCfg c;
     const char *e;
+    c.no_tc = getenv("RT_B200_NO_TC") != nullptr;
     c.no_const_rows = getenv("RT_B200_NO_CONST_ROWS") != nullptr;
     c.no_cost_order = getenv("RT_B200_NO_COST_ORDER") != nullptr;
     e = getenv("RT_B200_HEAVY_QUARTER_RAYS");
@@ -168,6 +169,7 @@ extern "C" int rt_scene_update(rt_scene *sc, const rt_sphere *sp, uint32_t n, vo
   sc->staged_pending = true;
   std::lock_guard<std::mutex> lk(sc->bvh_mu);
   sc->bvh_built = false;  // rebuilt by the next RT_FLAG_BVH render
+  sc->tc_built = false;   // ... and the tensor-core operand by the next render that uses it
   return RT_OK;
 }
 
@@ -178,7 +180,7 @@ extern "C" int rt_scene_destroy(rt_scene *sc) {
   cudaFree(sc->blob);
   if (sc->stage) cudaFreeHost(sc->stage);
   if (sc->staged) cudaEventDestroy(sc->staged);
-  cudaFree(sc->bvh_nodes); cudaFree(sc->bvh_prim);
+  cudaFree(sc->bvh_nodes); cudaFree(sc->bvh_prim); cudaFree(sc->tc_op);
   delete sc;
   return RT_OK;
 }
@@ -215,11 +217,30 @@ int rt_scene_ensure_bvh(const rt_scene *csc) {
   return RT_OK;
 }
 
+// Sphere operand of the tensor-core filter (rt_tc.cu), from the exact rows in the staging buffer.
+int rt_scene_ensure_tc(const rt_scene *csc) {
+  rt_scene *sc = const_cast<rt_scene *>(csc);
+  std::lock_guard<std::mutex> lk(sc->bvh_mu);
+  if (sc->tc_built) return RT_OK;
+  if (sc->staged_pending) CU(cudaEventSynchronize(sc->staged));
+  std::vector<float> op;
+  uint32_t tiles = 0;
+  tc_build_sphere_operand(reinterpret_cast<const double4 *>(sc->stage), sc->n, op, tiles);
+  float *d = nullptr;
+  CU(cudaMalloc(&d, op.size() * sizeof(float)));
+  CU_OR(cudaFree(d), cudaMemcpy(d, op.data(), op.size() * sizeof(float), cudaMemcpyHostToDevice));
+  cudaFree(sc->tc_op);
+  sc->tc_op = d; sc->tc_tiles = tiles; sc->tc_built = true;
+  return RT_OK;
+}
+
 SceneView rt_scene_view(const rt_scene *sc) {
   SceneView v;
   v.fast = sc->fast; v.exact = sc->exact; v.mat = sc->mat; v.aux = sc->aux; v.n = sc->n; v.n_pad = sc->n_pad;
   v.bvh_nodes = sc->bvh_built ? sc->bvh_nodes : nullptr;
   v.bvh_prim = sc->bvh_built ? sc->bvh_prim : nullptr;
+  v.tc_op = sc->tc_built ? sc->tc_op : nullptr;
+  v.tc_tiles = sc->tc_built ? sc->tc_tiles : 0u;
   return v;
 }
 
@@ -298,7 +319,7 @@ extern "C" int rt_frame_create(uint32_t width, uint32_t height, int32_t device, 
       (e = cudaMalloc(&f->partial, (size_t)f->npix * sizeof(float4))) != cudaSuccess ||
       (e = cudaMalloc(&f->rgb_words, quads * 12)) != cudaSuccess ||
       (e = cudaMalloc(&f->linear, (size_t)f->npix * 3 * sizeof(float))) != cudaSuccess ||
-      (e = cudaMalloc(&f->counters, 2 * sizeof(unsigned long long))) != cudaSuccess ||
+      (e = cudaMalloc(&f->counters, 4 * sizeof(unsigned long long))) != cudaSuccess ||
       (e = cudaMallocHost(&f->host_words, 4 * sizeof(unsigned long long))) != cudaSuccess ||
       (e = cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
     rt_frame_destroy(f);
@@ -353,6 +374,8 @@ static int check_cfg(const rt_config *cfg, const rt_frame *f) {
   if (cfg->samples_per_pixel == 0) return fail(RT_E_INVALID, "samples_per_pixel must be > 0");
   if ((cfg->flags & RT_FLAG_F32_HIT) && (cfg->flags & RT_FLAG_BVH))
     return fail(RT_E_INVALID, "RT_FLAG_F32_HIT works with the brute-force scan only");
+  if ((cfg->flags & RT_FLAG_SIMT_FILTER) && (cfg->flags & RT_FLAG_BVH))
+    return fail(RT_E_INVALID, "RT_FLAG_SIMT_FILTER selects between the two brute-force filters; not with RT_FLAG_BVH");
   if ((cfg->flags & RT_FLAG_NO_FILTER) && (cfg->flags & (RT_FLAG_BVH | RT_FLAG_F32_HIT)))
     return fail(RT_E_INVALID, "RT_FLAG_NO_FILTER works with the brute-force scan only");
   if (cfg->flags & ~RT_FLAG_ALL) return fail(RT_E_INVALID, "unknown flag bits 0x%x", cfg->flags & ~RT_FLAG_ALL);
@@ -389,6 +412,11 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
   // an empty world has no hierarchy to walk (its root box would be degenerate): brute force
   const bool use_bvh = (cfg->flags & RT_FLAG_BVH) != 0 && sc->n > 0;
   if (use_bvh && (rc = rt_scene_ensure_bvh(sc)) != RT_OK) return rc;
+  // the brute-force filter runs on the tensor cores when the sphere operand fits one CTA's shared
+  // memory (up to 1024 spheres); RT_FLAG_SIMT_FILTER / RT_B200_NO_TC keep the FFMA2 loop
+  const bool use_tc = !use_bvh && sc->n > 0 && (sc->n + 63u) / 64u <= kTcMaxTiles &&
+                      !(cfg->flags & (RT_FLAG_NO_FILTER | RT_FLAG_SIMT_FILTER)) && !env_cfg().no_tc;
+  if (use_tc && (rc = rt_scene_ensure_tc(sc)) != RT_OK) return rc;
   CamFrame cf;
   rt_derive_camera(cam, &cf);
   WaveParams w;
@@ -401,6 +429,7 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
   w.spp = cfg->samples_per_pixel; w.max_depth = cfg->max_depth;
   w.seed = cfg->seed; w.sample_offset = cfg->sample_offset;
   w.accum = f->accum; w.counter = f->counters;
+  w.status = reinterpret_cast<unsigned int *>(f->counters + 2);
   w.order = f->order_valid && f->order_heavy_only == use_bvh && !env_cfg().no_cost_order ? f->order : nullptr;
   w.heavy = f->heavy;
   f->last_n = sc->n;
@@ -426,6 +455,7 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
 
   uint32_t launches = 0;
   CU(cudaMemsetAsync(f->counters, 0, sizeof(unsigned long long), f->stream));
+  CU(cudaMemsetAsync(f->counters + 2, 0, sizeof(unsigned long long), f->stream));
   CU(cudaEventRecord(f->ev[0], f->stream));
   if (cfg->max_depth == 0) {
     // ray_color returns black at depth <= 0 (src/cpu/main.cc:16-17)
@@ -439,10 +469,12 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
     if ((rc = ensure_pool(f)) != RT_OK) return rc;
     WaveRunInfo info;
     CU(run_fused(w, f->pool, f->pool_slots, sc->host_fast.data(), use_bvh,
-                 (cfg->flags & RT_FLAG_F32_HIT) != 0, f->sm_count, f->smem_optin, f->stream, &info));
+                 (cfg->flags & RT_FLAG_F32_HIT) != 0, use_tc, f->sm_count, f->smem_optin, f->stream, &info));
     launches = info.launches;
+    f->last_tc = info.tensor_core_filter;
   }
   CU(cudaEventRecord(f->ev[1], f->stream));
+  CU(cudaMemcpyAsync(f->host_words + 2, f->counters + 2, sizeof(unsigned long long), cudaMemcpyDeviceToHost, f->stream));
   f->rendered = true;
   f->last_launches = launches;
   return RT_OK;
@@ -461,6 +493,7 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
   }
   if (caller_stream(f)) return RT_OK;  // asynchronous: timings through rt_frame_stats()
   CU(cudaStreamSynchronize(f->stream));
+  if (f->host_words[2]) return fail(RT_E_CUDA, "a tensor-core MMA of the filter never completed (bounded wait expired)");
   if (stats) CU(cudaEventElapsedTime(&stats->render_ms, f->ev[0], f->ev[1]));
   return RT_OK;
 }
@@ -571,6 +604,8 @@ extern "C" int rt_frame_stats(rt_frame *f, rt_stats *stats) {
   memset(stats, 0, sizeof *stats);
   if (f->rendered) {
     CU(cudaEventSynchronize(f->ev[1]));
+    CU(cudaStreamSynchronize(f->stream));
+    if (f->host_words[2]) return fail(RT_E_CUDA, "a tensor-core MMA of the filter never completed (bounded wait expired)");
     stats->samples = f->last_samples;
     stats->launches = f->last_launches;
     CU(cudaEventElapsedTime(&stats->render_ms, f->ev[0], f->ev[1]));

@@ -47,6 +47,10 @@ struct rt_scene {
   rtb::BvhNode *bvh_nodes = nullptr;
   uint32_t *bvh_prim = nullptr;
   uint32_t bvh_node_count = 0;
+  // sphere operand of the tensor-core filter, built on the host at the first render that uses it
+  bool tc_built = false;
+  float *tc_op = nullptr;
+  uint32_t tc_tiles = 0;
 };
 
 struct rt_frame {
@@ -56,8 +60,8 @@ struct rt_frame {
   float4 *partial;  // [npix]
   uint32_t *rgb_words;
   float *linear;
-  unsigned long long *counters;    // device: [0] work queue head, [1] ray total
-  unsigned long long *host_words;  // pinned: [1] ray total of the last finalise
+  unsigned long long *counters;    // device: [0] work queue head, [1] ray total, [2] tensor-core status
+  unsigned long long *host_words;  // pinned: [1] ray total of the last finalise, [2] tensor-core status
   cudaStream_t stream;      // stream in use (own_stream unless rt_frame_set_stream)
   cudaStream_t own_stream;
   cudaEvent_t ev[4];        // render begin/end, finalise begin/end
@@ -67,6 +71,7 @@ struct rt_frame {
   uint64_t last_samples;
   uint32_t last_launches;
   bool rendered, finalized;
+  bool last_tc;             // the last render ran the tensor-core filter
   void *pool;               // path-slot pool (allocated on first use)
   uint32_t pool_slots;
   // hand-out order of the next frame: pixels by descending cost of the frame rendered before
@@ -85,6 +90,7 @@ void rt_derive_camera(const rt_camera *c, CamFrame *f);
 rtb::CameraF32 rt_narrow_camera(const CamFrame &f, uint32_t W, uint32_t H, bool pixel_square);
 rtb::SceneView rt_scene_view(const rt_scene *sc);
 int rt_scene_ensure_bvh(const rt_scene *sc);
+int rt_scene_ensure_tc(const rt_scene *sc);
 
 // enqueue-only forms (no host synchronisation in the fused mode): the public entry points add the
 // synchronisation rule of rt_frame_set_stream on top

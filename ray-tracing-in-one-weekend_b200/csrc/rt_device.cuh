@@ -16,6 +16,8 @@ struct SceneView {
   const float2 *aux;     // [n] {1 / signed radius, material kind (integer bits)}
   const struct BvhNode *bvh_nodes;  // optional hierarchy (rt_bvh.cu); root = node 0
   const uint32_t *bvh_prim;         // sphere indices referenced by the leaves
+  const float *tc_op;               // sphere operand of the tensor-core filter (rt_tc.cu): [tc_tiles][4][2048 B]
+  uint32_t tc_tiles;                // 64-sphere tiles of it (0 = not built)
   uint32_t n;            // spheres in the hittable_list
   uint32_t n_pad;        // rows allocated: n rounded up to a multiple of kRowPad; padding rows can
                          // never pass the filter (w = -inf)

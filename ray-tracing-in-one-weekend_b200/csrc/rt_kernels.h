@@ -53,6 +53,7 @@ struct WaveParams {
   uint32_t no_filter;           // 1 = RT_FLAG_NO_FILTER: no f32 pre-test, every ray resolves every sphere in f64
   float4 *accum;                // [RT_SLICES][H*W] {sum r, sum g, sum b, ray segments}
   unsigned long long *counter;  // work-queue head (zeroed before the frame)
+  unsigned int *status;         // set to 1 if a tensor-core MMA never completed (bounded wait)
   const uint32_t *order;        // pixel hand-out order within a slice (nullptr = scan order)
   const uint32_t *heavy;        // leading pixels of `order` whose slices are all handed out first
   // pool of path slots (SoA, n_slots each)
@@ -69,6 +70,7 @@ struct WaveParams {
 
 // RT_B200_* experiment switches, read ONCE per process.
 struct EnvCfg {
+  bool no_tc;               // RT_B200_NO_TC: SIMT filter loop even where the tensor-core filter applies
   bool no_const_rows;       // RT_B200_NO_CONST_ROWS
   bool no_cost_order;       // RT_B200_NO_COST_ORDER
   int heavy_quarter_rays;   // RT_B200_HEAVY_QUARTER_RAYS, -1 unset
@@ -78,7 +80,7 @@ const EnvCfg &env_cfg();
 struct WaveRunInfo {
   uint32_t launches, n_slots;
   int rays_per_lane, grid;
-  bool rows_in_constant_bank, scene_in_smem;
+  bool rows_in_constant_bank, scene_in_smem, tensor_core_filter;
 };
 
 size_t wave_pool_bytes(uint32_t n_slots);
@@ -91,9 +93,16 @@ void build_bvh(const double4 *spheres, uint32_t n, std::vector<BvhNode> &nodes,
 // The persistent path kernel: one launch per frame; carves n_slots = grid * block * 2 out of the pool.
 // use_bvh: closest hit by BVH traversal (scene.bvh_nodes) instead of the brute-force filter.
 // f32_hit: candidate resolution in f32 like src/gpu/sphere.h (RT_FLAG_F32_HIT; brute force only).
+// use_tc: the brute-force filter as a tf32 contraction on the tensor cores (scene.tc_op), one CTA of
+// 512 threads per SM; else the SIMT filter loop (FFMA2, rows from the constant bank).
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
-                      bool use_bvh, bool f32_hit, int sm_count, size_t smem_optin_max, cudaStream_t st,
-                      WaveRunInfo *info);
+                      bool use_bvh, bool f32_hit, bool use_tc, int sm_count, size_t smem_optin_max,
+                      cudaStream_t st, WaveRunInfo *info);
+
+// Sphere operand of the tensor-core filter (rt_tc.cu): {cx, cy, cz, signed r} rows -> 3xTF32 split
+// feature rows in the K-major shared-memory layout the MMA descriptor names.
+void tc_build_sphere_operand(const double4 *exact, uint32_t n, std::vector<float> &out, uint32_t &tiles);
+constexpr uint32_t kTcMaxTiles = 16;  // 1024 spheres: the operand must fit one CTA's shared memory
 
 // Pixel hand-out order by descending cost (ray segments per sample in `partial`), stable.
 // heavy_only: only the heavy pixels move to the front, the others keep their scan order (BVH

@@ -24,6 +24,7 @@
 //   bvh_trace optional replacement of filter + resolve: closest hit through the host-built BVH.
 #include "rt_device.cuh"
 #include "rt_kernels.h"
+#include "rt_tc.cuh"
 
 #include <cstring>
 
@@ -247,7 +248,7 @@ __device__ __forceinline__ void record_root(WarpState &W, const uint32_t slot, c
 // group; the lane re-runs the f32 test on the group's G rows (same arithmetic as the filter), then
 // one exact test per round on the rows that pass.  Lanes that hold accepted roots of the SAME
 // slot in a round update its record one after the other (a single turn almost always).
-template <int G, bool F32HIT>
+template <int G, bool F32HIT, bool EXACT = false>
 __device__ __forceinline__ void resolve_entries(const WaveParams &P, WarpState &W, const uint32_t *glist,
                                                 const uint32_t n_entries, const double4 *exact,
                                                 const uint32_t lane) {
@@ -261,19 +262,25 @@ __device__ __forceinline__ void resolve_entries(const WaveParams &P, WarpState &
     if (idx < n_entries) {
       const uint32_t ent = idx < kListSmem ? W.list[idx] : glist[idx - kListSmem];
       slot = ent >> kGroupBits;
-      s0 = (ent & ((1u << kGroupBits) - 1u)) * (uint32_t)G;
       o = W.ro[slot];
       d = W.rd[slot];
-      const uint32_t skip = (uint32_t)__float_as_int(d.w);  // the sphere the ray just left, or -1
-      const float nod = -(o.x * d.x + o.y * d.y + o.z * d.z);
-      const float ox2 = 2.0f * o.x, oy2 = 2.0f * o.y, oz2 = 2.0f * o.z;
-      const float oot = (o.x * o.x + o.y * o.y + o.z * o.z) * (1.0f - RTB_FILTER_SLACK);
+      if (EXACT) {
+        // entries of the tensor-core filter name ONE sphere (the skip rule is applied there)
+        s0 = ent & ((1u << kGroupBits) - 1u);
+        m = 1u;
+      } else {
+        s0 = (ent & ((1u << kGroupBits) - 1u)) * (uint32_t)G;
+        const uint32_t skip = (uint32_t)__float_as_int(d.w);  // the sphere the ray just left, or -1
+        const float nod = -(o.x * d.x + o.y * d.y + o.z * d.z);
+        const float ox2 = 2.0f * o.x, oy2 = 2.0f * o.y, oz2 = 2.0f * o.z;
+        const float oot = (o.x * o.x + o.y * o.y + o.z * o.z) * (1.0f - RTB_FILTER_SLACK);
 #pragma unroll
-      for (int k = 0; k < G; ++k) {
-        const float4 S = __ldg(fast + s0 + k);
-        const float b = fmaf(S.x, d.x, fmaf(S.y, d.y, fmaf(S.z, d.z, nod)));
-        const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
-        if (e >= oot && s0 + (uint32_t)k != skip) m |= 1u << k;
+        for (int k = 0; k < G; ++k) {
+          const float4 S = __ldg(fast + s0 + k);
+          const float b = fmaf(S.x, d.x, fmaf(S.y, d.y, fmaf(S.z, d.z, nod)));
+          const float e = fmaf(S.x, ox2, fmaf(S.y, oy2, fmaf(S.z, oz2, fmaf(b, b, S.w))));
+          if (e >= oot && s0 + (uint32_t)k != skip) m |= 1u << k;
+        }
       }
     }
     const WRay ray = widen_ray(o, d, strict);
@@ -699,7 +706,7 @@ constexpr int kBvhMinB = RTW_MINB + 1;
 template <int G, bool CROWS, bool SMEM, bool BVH, bool F32HIT = false>
 __global__ void __launch_bounds__(kWBlock, BVH ? kBvhMinB : RTW_MINB)
 fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ ConstRows CR) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t s_bar;
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   WarpState &W = reinterpret_cast<WarpState *>(smem_raw)[warp];
@@ -741,6 +748,175 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
     }
     __syncwarp();
   }
+}
+
+// ================================================================ tensor-core filter (tcgen05)
+// @phase tc-filter
+// The brute-force filter as one tf32 contraction (formulation and operand layout: rt_tc.cu).  A
+// WARPGROUP works together: its 128 threads hold the 128 rays of an MMA's M dimension, thread <-> TMEM
+// lane.  Per block of rays (each lane's slot 0, then slot 1): every thread writes its ray's 32 feature
+// slots to its lane of the A columns; per tile of 64 spheres one elected thread issues the four K
+// steps and commits them to the group's mbarrier; every thread then reads ITS ray's 64 values back,
+// the group barrier frees D for the next tile, and the sign bits become candidate entries
+// {slot, sphere} appended to the warp's list with ballots -- while the next tile's MMAs run.
+constexpr int kTcBlock = 512, kTcWarps = kTcBlock / 32, kTcGroups = kTcBlock / 128;
+
+__device__ __forceinline__ void group_sync(const uint32_t gid) {
+  asm volatile("bar.sync %0, 128;" ::"r"(gid + 1u) : "memory");
+}
+__device__ __forceinline__ bool group_or(const uint32_t gid, const bool v) {
+  uint32_t r;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %2, 0;\n\tbar.red.or.pred p, %1, 128, q;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(r)
+      : "r"(gid + 1u), "r"((uint32_t)v)
+      : "memory");
+  return r != 0u;
+}
+
+__device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpState &W, uint32_t *glist,
+                                                   const uint32_t lane, const uint32_t gid, const bool issuer,
+                                                   uint64_t *bar, uint32_t &parity, const uint32_t tmem_g,
+                                                   const float *s_op) {
+  const uint32_t tiles = P.scene.tc_tiles;
+  const uint32_t lane_base = (((threadIdx.x >> 5) & 3u) * 32u) << 16;
+  const uint32_t a_tmem = tmem_g, d_tmem = tmem_g + 32u;
+  const uint32_t lt = (1u << lane) - 1u;
+  constexpr uint32_t gcap = 64u * kListGlobalPerSlot;
+  uint32_t wcnt = 0;  // entries recorded so far (warp-uniform)
+  // candidates of one 32-sphere half of a tile -> the warp's list, one ballot round per set bit
+  auto append = [&](uint32_t p, const uint32_t ebase) {
+    while (__any_sync(FULL, p != 0u)) {
+      const bool has = p != 0u;
+      const uint32_t b = (uint32_t)__ffs((int)p) - 1u;
+      p &= p - 1u;
+      const unsigned bal = __ballot_sync(FULL, has);
+      const uint32_t pos = wcnt + __popc(bal & lt);
+      if (has) {
+        if (pos < kListSmem) W.list[pos] = ebase + b;
+        else if (pos - kListSmem < gcap) glist[pos - kListSmem] = ebase + b;
+      }
+      wcnt += __popc(bal);
+    }
+  };
+#pragma unroll 1
+  for (uint32_t blk = 0; blk < 2u; ++blk) {
+    const uint32_t slot = lane + 32u * blk;
+    const float4 o = W.ro[slot], d = W.rd[slot];
+    const uint32_t skip = (uint32_t)__float_as_int(d.w);  // the sphere the ray just left, or -1
+    {
+      uint32_t sv[kTcK];
+      tc_ray_slots(o, d, sv);
+      TC_ST32(a_tmem + lane_base, sv);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    tc_fence_before();
+    group_sync(gid);  // the 128 rays' features are in tensor memory
+#pragma unroll 1
+    for (uint32_t t = 0; t < tiles; ++t) {
+      if (issuer) {
+        tc_fence_after();
+#pragma unroll
+        for (uint32_t j = 0; j < 4u; ++j)
+          tc_mma_ts(d_tmem, a_tmem + j * 8u, tc_smem_desc(s_op + ((size_t)t * 4u + j) * 512u), kTcIdesc, j);
+        tc_commit(bar);
+      }
+      // bounded wait: a tensor-core fault must not hang the GPU; after one expiry (bit 31) the thread
+      // stops waiting, the frame finishes with garbage and the host reports the status word
+      if (!(parity & 0x80000000u) && !mbar_wait_bounded(bar, parity & 1u)) {
+        atomicExch(P.status, 1u);
+        parity |= 0x80000000u;
+      }
+      parity ^= 1u;
+      tc_fence_after();
+      uint32_t v[kTcTile];
+      TC_LD32(d_tmem + lane_base, v, 0);
+      TC_LD32(d_tmem + lane_base + 32u, v, 32);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      group_sync(gid);  // D is free: the next tile's MMAs overlap the work below
+      uint32_t m0 = 0, m1 = 0;  // sign bits: 1 = e < 0 = miss
+#pragma unroll
+      for (int b = 31; b >= 0; --b) { m0 = __funnelshift_l(v[b], m0, 1); m1 = __funnelshift_l(v[32 + b], m1, 1); }
+      uint32_t p0 = ~m0, p1 = ~m1;
+      const uint32_t sk = skip - t * 64u;  // huge when the skipped sphere is not in this tile
+      if (sk < 32u) p0 &= ~(1u << sk);
+      else if (sk < 64u) p1 &= ~(1u << (sk - 32u));
+      const uint32_t ebase = (slot << kGroupBits) + t * 64u;
+      append(p0, ebase);
+      append(p1, ebase + 32u);
+    }
+  }
+  return wcnt;
+}
+
+// The persistent kernel with the tensor-core filter: ONE CTA of 512 threads (four warpgroups) per
+// SM -- the sphere operand (8 KB per 64 spheres) lives once per SM in shared memory and the SM's
+// 512 TMEM columns are split four ways (32 columns of ray features + 64 of accumulators per group).
+// Shade and resolve are the warp-level phases of fused_kernel, unchanged.
+template <bool SMEM, bool F32HIT>
+__global__ void __launch_bounds__(kTcBlock, 1)
+fused_tc_kernel(const __grid_constant__ WaveParams P) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ __align__(8) uint64_t s_mma[kTcGroups];
+  __shared__ uint32_t s_tmem;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, gid = warp >> 2;
+  const uint32_t op_floats = P.scene.tc_tiles * 4u * 512u;
+  float *s_op = reinterpret_cast<float *>(smem_raw);
+  unsigned char *after_op = smem_raw + (size_t)op_floats * 4u;
+  WarpState &W = reinterpret_cast<WarpState *>(after_op)[warp];
+  {
+    const float4 *src = reinterpret_cast<const float4 *>(P.scene.tc_op);
+    float4 *dst = reinterpret_cast<float4 *>(s_op);
+    for (uint32_t i = threadIdx.x; i < op_floats / 4u; i += kTcBlock) dst[i] = __ldg(src + i);
+  }
+  if (threadIdx.x < kTcGroups) mbar_init(&s_mma[threadIdx.x], 1);
+  if (warp == 0) tmem_alloc(&s_tmem, 512);
+  // the operand was written through the generic proxy; the tensor core reads it through the async one
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  const double4 *exact = P.scene.exact;
+  const float4 *mat = P.scene.mat;
+  const float2 *aux = P.scene.aux;
+  if (SMEM) stage_hit_rows(P, after_op + kTcWarps * sizeof(WarpState), &s_bar, exact, mat, aux);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_g = s_tmem + gid * 128u;
+  const bool issuer = (threadIdx.x & 127u) == 0u;
+  const uint32_t npix = P.width * P.height;
+  const uint32_t total_items = npix * P.n_orders;  // < 2^32: 2^26 pixels x 64 slices at most
+  const uint32_t stride = P.n_slots / 2u;
+  const uint32_t base = blockIdx.x * kTcBlock + threadIdx.x;  // grid * block == stride
+  uint32_t *glist = P.glist + (size_t)(blockIdx.x * kTcWarps + warp) * (64u * kListGlobalPerSlot);
+#pragma unroll 1
+  for (int r = 0; r < 2; ++r) {
+    const uint32_t i = base + r * stride, slot = lane + 32u * r;
+    P.thr[i] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));  // depth 0: needs a path
+    P.acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    P.it[i] = make_uint4(kNoItem, 0u, 0u, 0u);
+    W.ro[slot] = make_float4(0.f, 0.f, 0.f, -1.f);
+    W.rd[slot] = make_float4(0.f, 1.f, 0.f, __int_as_float(-1));
+    W.key[slot] = kInfKey;
+    W.id[slot] = -1;
+  }
+  uint32_t parity = 0;
+  for (;;) {
+    uint32_t live = 0;
+#pragma unroll 1
+    for (int r = 0; r < 2; ++r)
+      live += shade_slot<F32HIT>(P, W, lane + 32u * r, base + r * stride, exact, mat, aux, npix, total_items);
+    if (!group_or(gid, live != 0u)) break;  // the four warps of a group leave together
+    __syncwarp();
+    const uint32_t n_entries = filter_rays_tc(P, W, glist, lane, gid, issuer, &s_mma[gid], parity, tmem_g, s_op);
+    __syncwarp();
+    if (n_entries <= kListSmem + 64u * kListGlobalPerSlot) resolve_entries<RTW_G, F32HIT, true>(P, W, glist, n_entries, exact, lane);
+    else resolve_scan<F32HIT>(P, W, exact, lane);
+    __syncwarp();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(s_tmem, 512);
 }
 
 // ================================================================ host side
@@ -799,11 +975,51 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
   return cudaGetLastError();
 }
 
+// one CTA of 512 threads per SM; shared memory = sphere operand | 16 warp states | per-hit rows
+static cudaError_t launch_fused_tc(WaveParams &p, void *pool, uint32_t pool_slots, bool f32hit, int sm_count,
+                                   size_t smem_optin_max, bool *in_smem_out, int *grid_out, cudaStream_t st) {
+  const size_t op_bytes = (size_t)p.scene.tc_tiles * 8192u;
+  const size_t warp_smem = (size_t)kTcWarps * sizeof(WarpState);
+  const size_t scene_smem = (size_t)p.scene.n_pad * 56;
+  const bool in_smem = op_bytes + warp_smem + scene_smem <= smem_optin_max;
+  const size_t smem = op_bytes + warp_smem + (in_smem ? scene_smem : 0);
+  if (smem > smem_optin_max) return cudaErrorInvalidValue;
+  const int grid = sm_count;
+  const uint32_t n_slots = (uint32_t)grid * kTcBlock * 2u;
+  if (n_slots > pool_slots) return cudaErrorInvalidValue;
+  wave_carve(p, pool, n_slots);
+  *grid_out = grid; *in_smem_out = in_smem;
+#define RTW_TC(SM_, F32_)                                                                          \
+  do {                                                                                             \
+    auto k = fused_tc_kernel<SM_, F32_>;                                                           \
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    if (e != cudaSuccess) return e;                                                                \
+    k<<<grid, kTcBlock, smem, st>>>(p);                                                            \
+  } while (0)
+  if (in_smem && f32hit) RTW_TC(true, true);
+  else if (in_smem) RTW_TC(true, false);
+  else if (f32hit) RTW_TC(false, true);
+  else RTW_TC(false, false);
+#undef RTW_TC
+  return cudaGetLastError();
+}
+
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
-                      bool use_bvh, bool f32_hit, int sm_count, size_t smem_optin_max, cudaStream_t st,
-                      WaveRunInfo *info) {
+                      bool use_bvh, bool f32_hit, bool use_tc, int sm_count, size_t smem_optin_max,
+                      cudaStream_t st, WaveRunInfo *info) {
   if (use_bvh && !p.scene.bvh_nodes) return cudaErrorInvalidValue;
   if (use_bvh && f32_hit) return cudaErrorInvalidValue;
+  if (use_tc) {
+    if (use_bvh || !p.scene.tc_op || p.scene.tc_tiles == 0 || p.scene.tc_tiles > kTcMaxTiles) return cudaErrorInvalidValue;
+    bool in_smem = false;
+    int grid = 0;
+    cudaError_t e = launch_fused_tc(p, pool, pool_slots, f32_hit, sm_count, smem_optin_max, &in_smem, &grid, st);
+    if (info) {
+      info->launches = 1; info->n_slots = p.n_slots; info->rays_per_lane = 2; info->grid = grid;
+      info->rows_in_constant_bank = false; info->scene_in_smem = in_smem; info->tensor_core_filter = true;
+    }
+    return e;
+  }
   static thread_local ConstRows cr;  // 16 KB kernel parameter; frames may render from several host threads
   const bool crows = !use_bvh && host_rows && p.scene.n_pad + 2 * kRowTail <= (uint32_t)kConstRows &&
                      !env_cfg().no_const_rows;
@@ -820,7 +1036,7 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
                                         sm_count, &grid, st);
   if (info) {
     info->launches = 1; info->n_slots = p.n_slots; info->rays_per_lane = 2; info->grid = grid;
-    info->rows_in_constant_bank = crows; info->scene_in_smem = in_smem;
+    info->rows_in_constant_bank = crows; info->scene_in_smem = in_smem; info->tensor_core_filter = false;
   }
   return e;
 }
