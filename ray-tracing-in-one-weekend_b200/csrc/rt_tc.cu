@@ -146,9 +146,7 @@ tc_filter_probe_kernel(const float4 *__restrict__ ray_o, const float4 *__restric
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         tc_fence_before();
         __syncthreads();  // D is free: the next tile's MMAs may overwrite it while the masks are built
-        uint32_t m0 = 0, m1 = 0;
-#pragma unroll
-        for (int b = 31; b >= 0; --b) { m0 = __funnelshift_l(v[b], m0, 1); m1 = __funnelshift_l(v[32 + b], m1, 1); }
+        const uint32_t m0 = tc_sign_mask(v, 0), m1 = tc_sign_mask(v, 32);
         // m has the SIGN bits: bit b = 1 -> e < 0 -> miss
         const unsigned long long pass = ~((unsigned long long)m1 << 32 | m0);
         if (ray < n_rays && rep == 0) {

@@ -44,10 +44,11 @@ __device__ __forceinline__ uint64_t tc_smem_desc(const void *p) {
 // instruction descriptor: D = f32, A = B = tf32, both K-major, M = 128, N = 64
 constexpr uint32_t kTcIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTcTile >> 3) << 17) | ((128u >> 4) << 24);
 
-// bounded wait: a wrong descriptor must not hang the GPU box
+// bounded wait: a wrong descriptor must not hang the GPU box.  try_wait suspends the thread in
+// hardware for a system-dependent time, so the loop spins a handful of times; 2^22 expiries
+// (seconds) mean the MMA will never complete.
 __device__ __forceinline__ bool mbar_wait_bounded(uint64_t *bar, uint32_t parity) {
-  const long long t0 = clock64();
-  for (;;) {
+  for (uint32_t spins = 0; spins < (1u << 22); ++spins) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
@@ -55,8 +56,20 @@ __device__ __forceinline__ bool mbar_wait_bounded(uint64_t *bar, uint32_t parity
         : "r"(smem_addr(bar)), "r"(parity)
         : "memory");
     if (ok) return true;
-    if (clock64() - t0 > 200000000ll) return false;  // ~0.1 s
   }
+  return false;
+}
+
+// sign bits of 32 accumulator values -> one word (bit b = sign of v[o + b]).  Eight independent
+// chains of funnel shifts (one per byte) instead of one chain of 32: with 16 warps per SM the
+// latency of a dependent chain is not hidden.
+__device__ __forceinline__ uint32_t tc_sign_mask(const uint32_t (&v)[kTcTile], const int o) {
+  uint32_t m[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+  for (int b = 7; b >= 0; --b)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) m[k] = __funnelshift_l(v[o + 8 * k + b], m[k], 1);
+  return m[0] | (m[1] << 8) | (m[2] << 16) | (m[3] << 24);
 }
 
 // psi(o, d) -> the ray's 32 K slots {hi, lo, hi} x 9, k (hi, lo), 1, 1, 0

@@ -777,7 +777,7 @@ __device__ __forceinline__ bool group_or(const uint32_t gid, const bool v) {
 __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpState &W, uint32_t *glist,
                                                    const uint32_t lane, const uint32_t gid, const bool issuer,
                                                    uint64_t *bar, uint32_t &parity, const uint32_t tmem_g,
-                                                   const float *s_op) {
+                                                   const uint64_t desc0) {
   const uint32_t tiles = P.scene.tc_tiles;
   const uint32_t lane_base = (((threadIdx.x >> 5) & 3u) * 32u) << 16;
   const uint32_t a_tmem = tmem_g, d_tmem = tmem_g + 32u;
@@ -816,9 +816,10 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
     for (uint32_t t = 0; t < tiles; ++t) {
       if (issuer) {
         tc_fence_after();
+        // descriptors of the tile's four K slabs: consecutive 2048-byte slabs = +128 in the address field
+        const uint64_t dt = desc0 + (uint64_t)(t * 4u) * 128u;
 #pragma unroll
-        for (uint32_t j = 0; j < 4u; ++j)
-          tc_mma_ts(d_tmem, a_tmem + j * 8u, tc_smem_desc(s_op + ((size_t)t * 4u + j) * 512u), kTcIdesc, j);
+        for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * 128u, kTcIdesc, j);
         tc_commit(bar);
       }
       // bounded wait: a tensor-core fault must not hang the GPU; after one expiry (bit 31) the thread
@@ -835,10 +836,7 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       tc_fence_before();
       group_sync(gid);  // D is free: the next tile's MMAs overlap the work below
-      uint32_t m0 = 0, m1 = 0;  // sign bits: 1 = e < 0 = miss
-#pragma unroll
-      for (int b = 31; b >= 0; --b) { m0 = __funnelshift_l(v[b], m0, 1); m1 = __funnelshift_l(v[32 + b], m1, 1); }
-      uint32_t p0 = ~m0, p1 = ~m1;
+      uint32_t p0 = ~tc_sign_mask(v, 0), p1 = ~tc_sign_mask(v, 32);  // sign bit 1 = e < 0 = miss
       const uint32_t sk = skip - t * 64u;  // huge when the skipped sphere is not in this tile
       if (sk < 32u) p0 &= ~(1u << sk);
       else if (sk < 64u) p1 &= ~(1u << (sk - 32u));
@@ -900,6 +898,7 @@ fused_tc_kernel(const __grid_constant__ WaveParams P) {
     W.key[slot] = kInfKey;
     W.id[slot] = -1;
   }
+  const uint64_t desc0 = tc_smem_desc(s_op);
   uint32_t parity = 0;
   for (;;) {
     uint32_t live = 0;
@@ -908,7 +907,7 @@ fused_tc_kernel(const __grid_constant__ WaveParams P) {
       live += shade_slot<F32HIT>(P, W, lane + 32u * r, base + r * stride, exact, mat, aux, npix, total_items);
     if (!group_or(gid, live != 0u)) break;  // the four warps of a group leave together
     __syncwarp();
-    const uint32_t n_entries = filter_rays_tc(P, W, glist, lane, gid, issuer, &s_mma[gid], parity, tmem_g, s_op);
+    const uint32_t n_entries = filter_rays_tc(P, W, glist, lane, gid, issuer, &s_mma[gid], parity, tmem_g, desc0);
     __syncwarp();
     if (n_entries <= kListSmem + 64u * kListGlobalPerSlot) resolve_entries<RTW_G, F32HIT, true>(P, W, glist, n_entries, exact, lane);
     else resolve_scan<F32HIT>(P, W, exact, lane);
