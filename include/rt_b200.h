@@ -209,11 +209,12 @@ int rt_measure_fp32_peak(int32_t device, float *tflops, float *sm_clock_mhz_est)
 /* --- measurement / validation aid: the brute-force filter written as ONE tf32 contraction on the
  *     tensor cores (tcgen05.mma, accumulators in tensor memory) on `n` rays
  *     {ox, oy, oz, |d| > 0}, {unit d, -} against a scene of up to 1024 spheres.  masks: HOST
- *     [n][tiles] 64-bit words, bit b of word t set = sphere 64 t + b passes; values (optional): HOST
- *     [n_values][tiles][64] raw filter values; ms: device time of `repeats` passes over the rays.
- *     Not part of the render path. */
+ *     [n][tiles] 64-bit words, bit b of word t set = sphere tile_spheres * t + b passes; values
+ *     (optional): HOST [n_values][tiles][tile_spheres] raw filter values; ms: device time of
+ *     `repeats` passes over the rays.  Not part of the render path. */
 int rt_tc_filter_probe(const rt_scene *, const float *ray_o, const float *ray_d, uint32_t n, uint64_t *masks,
-                       uint32_t *tiles, float *values, uint32_t n_values, uint32_t repeats, float *ms);
+                       uint32_t *tiles, uint32_t *tile_spheres, float *values, uint32_t n_values,
+                       uint32_t repeats, float *ms);
 
 /* --- output stage (the step after the path): "P3\nW H\n255\n" + "r g b\n" per pixel, rows
  *     top->bottom (src/cpu/main.cc:109, color.h:20-22; the multi-threaded program's loop,

@@ -350,22 +350,22 @@ class Multi:
 
 def tc_filter_probe(scene: Scene, ray_o: np.ndarray, ray_d: np.ndarray, n_values: int = 0, repeats: int = 1):
     """The filter as a tf32 contraction on the tensor cores (rt_tc_filter_probe).
-    -> (pass mask bool [n][tiles * 64], raw values f32 [n_values][tiles * 64] | None, ms)"""
+    -> (pass mask bool [n][tiles * T], raw values f32 [n_values][tiles * T] | None, ms); T = spheres per tile"""
     ray_o = np.ascontiguousarray(ray_o, np.float32).reshape(-1, 4)
     ray_d = np.ascontiguousarray(ray_d, np.float32).reshape(-1, 4)
     n = len(ray_o)
-    tiles_max = 16
+    tiles_max = 32
     masks = np.zeros((n, tiles_max), np.uint64)
     vals = np.zeros((n_values, tiles_max * 64), np.float32) if n_values else None
-    tiles, ms = C.c_uint32(), C.c_float()
+    tiles, tsz, ms = C.c_uint32(), C.c_uint32(), C.c_float()
     _check(lib().rt_tc_filter_probe(scene._h, C.c_void_p(ray_o.ctypes.data), C.c_void_p(ray_d.ctypes.data),
-                                    C.c_uint32(n), C.c_void_p(masks.ctypes.data), C.byref(tiles),
+                                    C.c_uint32(n), C.c_void_p(masks.ctypes.data), C.byref(tiles), C.byref(tsz),
                                     C.c_void_p(vals.ctypes.data) if vals is not None else None,
                                     C.c_uint32(n_values), C.c_uint32(repeats), C.byref(ms)))
-    t = tiles.value
+    t, T = tiles.value, tsz.value
     m = masks.reshape(-1)[: n * t].reshape(n, t)
-    bits = np.unpackbits(m.view(np.uint8).reshape(n, t, 8), axis=2, bitorder="little").reshape(n, t * 64).astype(bool)
-    v = vals.reshape(-1)[: n_values * t * 64].reshape(n_values, t * 64) if vals is not None else None
+    bits = np.unpackbits(m.view(np.uint8).reshape(n, t, 8), axis=2, bitorder="little")[:, :, :T].reshape(n, t * T).astype(bool)
+    v = vals.reshape(-1)[: n_values * t * T].reshape(n_values, t * T) if vals is not None else None
     return bits, v, ms.value
 
 

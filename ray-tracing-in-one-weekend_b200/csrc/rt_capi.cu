@@ -413,8 +413,9 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
   const bool use_bvh = (cfg->flags & RT_FLAG_BVH) != 0 && sc->n > 0;
   if (use_bvh && (rc = rt_scene_ensure_bvh(sc)) != RT_OK) return rc;
   // the brute-force filter runs on the tensor cores when the sphere operand fits one CTA's shared
-  // memory (up to 1024 spheres); RT_FLAG_SIMT_FILTER / RT_B200_NO_TC keep the FFMA2 loop
-  const bool use_tc = !use_bvh && sc->n > 0 && (sc->n + 63u) / 64u <= kTcMaxTiles &&
+  // memory (32 to 1024 spheres); RT_FLAG_SIMT_FILTER / RT_B200_NO_TC keep the FFMA2 loop
+  // (a handful of spheres is a single trip of the FFMA2 loop: not worth a tensor-core round trip)
+  const bool use_tc = !use_bvh && sc->n >= 32u && sc->n <= kTcMaxSpheres &&
                       !(cfg->flags & (RT_FLAG_NO_FILTER | RT_FLAG_SIMT_FILTER)) && !env_cfg().no_tc;
   if (use_tc && (rc = rt_scene_ensure_tc(sc)) != RT_OK) return rc;
   CamFrame cf;

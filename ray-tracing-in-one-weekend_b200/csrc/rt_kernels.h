@@ -102,7 +102,7 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
 // Sphere operand of the tensor-core filter (rt_tc.cu): {cx, cy, cz, signed r} rows -> 3xTF32 split
 // feature rows in the K-major shared-memory layout the MMA descriptor names.
 void tc_build_sphere_operand(const double4 *exact, uint32_t n, std::vector<float> &out, uint32_t &tiles);
-constexpr uint32_t kTcMaxTiles = 16;  // 1024 spheres: the operand must fit one CTA's shared memory
+constexpr uint32_t kTcMaxSpheres = 960;  // the operand (128 B per sphere) must fit one CTA's shared memory
 
 // Pixel hand-out order by descending cost (ray segments per sample in `partial`), stable.
 // heavy_only: only the heavy pixels move to the front, the others keep their scan order (BVH

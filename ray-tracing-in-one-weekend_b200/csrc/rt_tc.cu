@@ -44,7 +44,7 @@ static void split_tf32(double x, float &hi, float &lo) {
   lo = tf32_trunc((float)(x - (double)hi));
 }
 
-// Canonical K-major, no-swizzle layout of one [64 spheres x 8 K] slab (2048 B): core matrices of
+// Canonical K-major, no-swizzle layout of one [kTcTile spheres x 8 K] slab (32 B per sphere): core matrices of
 // 8 rows x 16 B; the two K halves of a row group 128 B apart (LBO), row groups 256 B apart (SBO).
 static size_t slab_offset(int row, int k) {
   return (size_t)(row / 8) * 256 + (size_t)(k / 4) * 128 + (size_t)(row % 8) * 16 + (size_t)(k % 4) * 4;
@@ -54,7 +54,7 @@ static size_t slab_offset(int row, int k) {
 void tc_build_sphere_operand(const double4 *exact, uint32_t n, std::vector<float> &out, uint32_t &tiles) {
   tiles = (n + kTcTile - 1) / kTcTile;
   if (tiles == 0) tiles = 1;
-  out.assign((size_t)tiles * 4 * 512, 0.0f);
+  out.assign((size_t)tiles * 4 * kTcSlabFloats, 0.0f);
   for (uint32_t s = 0; s < tiles * kTcTile; ++s) {
     double f[11];
     if (s < n) {
@@ -84,7 +84,7 @@ void tc_build_sphere_operand(const double4 *exact, uint32_t n, std::vector<float
     }
     const uint32_t tile = s / kTcTile, row = s % kTcTile;
     for (int k = 0; k < kTcK; ++k) {
-      const size_t off = ((size_t)tile * 4 + k / 8) * 2048 + slab_offset((int)row, k % 8);
+      const size_t off = ((size_t)tile * 4 + k / 8) * (kTcSlabFloats * 4) + slab_offset((int)row, k % 8);
       out[off / 4] = slot[k];
     }
   }
@@ -93,7 +93,7 @@ void tc_build_sphere_operand(const double4 *exact, uint32_t n, std::vector<float
 // ---------------------------------------------------------------- probe kernel
 // One warpgroup (128 threads = 128 rays per block of rays) per CTA, one CTA per SM.  For every
 // block of 128 rays: features -> TMEM, then per tile of 64 spheres 4 MMA steps, read back, fold
-// the sign bits into masks[ray][tile] (bit b set: sphere tile * 64 + b passes).  `values`
+// the sign bits into masks[ray][tile] (bit b set: sphere tile * kTcTile + b passes).  `values`
 // (optional) receives the raw e of the first `n_values` rays for the error measurement.
 __global__ void __launch_bounds__(128, 1)
 tc_filter_probe_kernel(const float4 *__restrict__ ray_o, const float4 *__restrict__ ray_d, uint32_t n_rays,
@@ -104,7 +104,7 @@ tc_filter_probe_kernel(const float4 *__restrict__ ray_o, const float4 *__restric
   __shared__ uint32_t s_tmem;
   float *s_op = reinterpret_cast<float *>(smem_raw);
   const uint32_t tid = threadIdx.x, warp = tid >> 5;
-  for (uint32_t i = tid; i < tiles * 4u * 512u; i += 128u) s_op[i] = sphere_op[i];
+  for (uint32_t i = tid; i < tiles * 4u * (uint32_t)kTcSlabFloats; i += 128u) s_op[i] = sphere_op[i];
   if (tid == 0) mbar_init(&s_bar, 1);
   if (warp == 0) tmem_alloc(&s_tmem, 128);
   // generic-proxy writes of the operand must be visible to the tensor core's async proxy
@@ -134,21 +134,20 @@ tc_filter_probe_kernel(const float4 *__restrict__ ray_o, const float4 *__restric
           tc_fence_after();
 #pragma unroll
           for (uint32_t j = 0; j < 4; ++j)
-            tc_mma_ts(d_tmem, a_tmem + j * 8u, tc_smem_desc(s_op + ((size_t)t * 4 + j) * 512), kTcIdesc, j);
+            tc_mma_ts(d_tmem, a_tmem + j * 8u, tc_smem_desc(s_op + ((size_t)t * 4 + j) * kTcSlabFloats), kTcIdesc, j);
           tc_commit(&s_bar);
         }
         ok = mbar_wait_bounded(&s_bar, parity);
         parity ^= 1u;
         tc_fence_after();
         uint32_t v[kTcTile];
-        TC_LD32(d_tmem + lane_base, v, 0);
-        TC_LD32(d_tmem + lane_base + 32u, v, 32);
+        TC_LD_TILE(d_tmem + lane_base, v);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         tc_fence_before();
         __syncthreads();  // D is free: the next tile's MMAs may overwrite it while the masks are built
-        const uint32_t m0 = tc_sign_mask(v, 0), m1 = tc_sign_mask(v, 32);
-        // m has the SIGN bits: bit b = 1 -> e < 0 -> miss
-        const unsigned long long pass = ~((unsigned long long)m1 << 32 | m0);
+        uint32_t p0, p1;
+        tc_pass_bits(v, p0, p1);
+        const unsigned long long pass = (unsigned long long)p1 << 32 | p0;
         if (ray < n_rays && rep == 0) {
           masks[(size_t)ray * tiles + t] = pass;
           if (values && ray < n_values)
@@ -169,9 +168,10 @@ using namespace rtb;
 // {o.xyz, |d| > 0} / {unit d} against the scene.  masks: HOST [n][tiles] 64-bit pass masks;
 // values: optional HOST [n_values][tiles][64] raw e; ms: device time of `repeats` passes over the rays.
 extern "C" int rt_tc_filter_probe(const rt_scene *sc, const float *ray_o, const float *ray_d, uint32_t n,
-                                  uint64_t *masks, uint32_t *tiles_out, float *values, uint32_t n_values,
-                                  uint32_t repeats, float *ms) {
-  if (!sc || !ray_o || !ray_d || !masks || !tiles_out) return rt_fail(RT_E_INVALID, "NULL argument");
+                                  uint64_t *masks, uint32_t *tiles_out, uint32_t *tile_spheres, float *values,
+                                  uint32_t n_values, uint32_t repeats, float *ms) {
+  if (!sc || !ray_o || !ray_d || !masks || !tiles_out || !tile_spheres) return rt_fail(RT_E_INVALID, "NULL argument");
+  *tile_spheres = (uint32_t)kTcTile;
   if (sc->n == 0 || sc->n > 1024u) return rt_fail(RT_E_INVALID, "the probe keeps the sphere operand in shared memory: 1..1024 spheres");
   CU(cudaSetDevice(sc->device));
   const double4 *e = reinterpret_cast<const double4 *>(sc->stage);  // exact rows sit first in the staging buffer

@@ -9,7 +9,13 @@
 namespace rtb {
 
 constexpr int kTcK = 32;          // K slots (4 MMA steps of 8)
-constexpr int kTcTile = 64;       // spheres per MMA (N)
+#ifndef RTW_TC_TILE
+#define RTW_TC_TILE 64
+#endif
+constexpr int kTcTile = RTW_TC_TILE;  // spheres per MMA (N): 48 or 64 (a warpgroup's TMEM share holds 32 + N columns)
+static_assert(kTcTile == 48 || kTcTile == 64, "accumulator tile of 48 or 64 spheres");
+constexpr int kTcSlabFloats = kTcTile * 8;   // one [tile x 8 K] slab of the sphere operand
+constexpr int kTcSlabUnits = kTcTile * 2;    // ... in 16-byte units of the descriptor's address field
 constexpr float kTcKappa = 1.52587890625e-05f;  // 2^-16: bound of the contraction's error in units of A_s + B_r
 
 // ---------------------------------------------------------------- device helpers (tcgen05)
@@ -63,13 +69,24 @@ __device__ __forceinline__ bool mbar_wait_bounded(uint64_t *bar, uint32_t parity
 // sign bits of 32 accumulator values -> one word (bit b = sign of v[o + b]).  Eight independent
 // chains of funnel shifts (one per byte) instead of one chain of 32: with 16 warps per SM the
 // latency of a dependent chain is not hidden.
+template <int BYTES = 4>
 __device__ __forceinline__ uint32_t tc_sign_mask(const uint32_t (&v)[kTcTile], const int o) {
-  uint32_t m[4] = {0u, 0u, 0u, 0u};
+  uint32_t m[BYTES];
+#pragma unroll
+  for (int k = 0; k < BYTES; ++k) m[k] = 0u;
 #pragma unroll
   for (int b = 7; b >= 0; --b)
 #pragma unroll
-    for (int k = 0; k < 4; ++k) m[k] = __funnelshift_l(v[o + 8 * k + b], m[k], 1);
-  return m[0] | (m[1] << 8) | (m[2] << 16) | (m[3] << 24);
+    for (int k = 0; k < BYTES; ++k) m[k] = __funnelshift_l(v[o + 8 * k + b], m[k], 1);
+  uint32_t r = m[0];
+#pragma unroll
+  for (int k = 1; k < BYTES; ++k) r |= m[k] << (8 * k);
+  return r;
+}
+// pass bits of a tile: low word = spheres 0..31, high word = spheres 32..kTcTile-1 (sign bit 1 = miss)
+__device__ __forceinline__ void tc_pass_bits(const uint32_t (&v)[kTcTile], uint32_t &p0, uint32_t &p1) {
+  p0 = ~tc_sign_mask<4>(v, 0);
+  p1 = kTcTile == 64 ? ~tc_sign_mask<4>(v, 32) : (~tc_sign_mask<2>(v, 32) & 0xffffu);
 }
 
 // psi(o, d) -> the ray's 32 K slots {hi, lo, hi} x 9, k (hi, lo), 1, 1, 0
@@ -120,5 +137,23 @@ __device__ __forceinline__ void tc_ray_slots(const float4 o, const float4 d, uin
                : "r"(addr)                                                                                  \
                : "memory")
 
+
+#define TC_LD16(addr, v, o)                                                                                 \
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, " \
+               "%12, %13, %14, %15}, [%16];"                                                                \
+               : "=r"(v[o + 0]), "=r"(v[o + 1]), "=r"(v[o + 2]), "=r"(v[o + 3]), "=r"(v[o + 4]),            \
+                 "=r"(v[o + 5]), "=r"(v[o + 6]), "=r"(v[o + 7]), "=r"(v[o + 8]), "=r"(v[o + 9]),            \
+                 "=r"(v[o + 10]), "=r"(v[o + 11]), "=r"(v[o + 12]), "=r"(v[o + 13]), "=r"(v[o + 14]),       \
+                 "=r"(v[o + 15])                                                                            \
+               : "r"(addr)                                                                                  \
+               : "memory")
+
+// this thread's row of an accumulator tile -> registers
+#define TC_LD_TILE(addr, v)                                      \
+  do {                                                           \
+    TC_LD32((addr), v, 0);                                       \
+    if (kTcTile == 64) { TC_LD32((addr) + 32u, v, 32); }         \
+    else { TC_LD16((addr) + 32u, v, 32); }                       \
+  } while (0)
 
 }  // namespace rtb

@@ -759,7 +759,12 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
 // steps and commits them to the group's mbarrier; every thread then reads ITS ray's 64 values back,
 // the group barrier frees D for the next tile, and the sign bits become candidate entries
 // {slot, sphere} appended to the warp's list with ballots -- while the next tile's MMAs run.
-constexpr int kTcBlock = 512, kTcWarps = kTcBlock / 32, kTcGroups = kTcBlock / 128;
+#ifndef RTW_TC_BLOCK
+#define RTW_TC_BLOCK 640
+#endif
+constexpr int kTcBlock = RTW_TC_BLOCK, kTcWarps = kTcBlock / 32, kTcGroups = kTcBlock / 128;
+constexpr uint32_t kTcGroupCols = 32u + (uint32_t)kTcTile;  // TMEM columns of a warpgroup: ray features + one accumulator tile
+static_assert(kTcGroups * kTcGroupCols <= 512u, "the warpgroups' tensor-memory shares exceed the SM's 512 columns");
 
 __device__ __forceinline__ void group_sync(const uint32_t gid) {
   asm volatile("bar.sync %0, 128;" ::"r"(gid + 1u) : "memory");
@@ -816,10 +821,10 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
     for (uint32_t t = 0; t < tiles; ++t) {
       if (issuer) {
         tc_fence_after();
-        // descriptors of the tile's four K slabs: consecutive 2048-byte slabs = +128 in the address field
-        const uint64_t dt = desc0 + (uint64_t)(t * 4u) * 128u;
+        // descriptors of the tile's four K slabs: consecutive slabs = + kTcSlabUnits in the address field
+        const uint64_t dt = desc0 + (uint64_t)(t * 4u) * (uint64_t)kTcSlabUnits;
 #pragma unroll
-        for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * 128u, kTcIdesc, j);
+        for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * (uint64_t)kTcSlabUnits, kTcIdesc, j);
         tc_commit(bar);
       }
       // bounded wait: a tensor-core fault must not hang the GPU; after one expiry (bit 31) the thread
@@ -831,16 +836,16 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
       parity ^= 1u;
       tc_fence_after();
       uint32_t v[kTcTile];
-      TC_LD32(d_tmem + lane_base, v, 0);
-      TC_LD32(d_tmem + lane_base + 32u, v, 32);
+      TC_LD_TILE(d_tmem + lane_base, v);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       tc_fence_before();
       group_sync(gid);  // D is free: the next tile's MMAs overlap the work below
-      uint32_t p0 = ~tc_sign_mask(v, 0), p1 = ~tc_sign_mask(v, 32);  // sign bit 1 = e < 0 = miss
-      const uint32_t sk = skip - t * 64u;  // huge when the skipped sphere is not in this tile
+      uint32_t p0, p1;
+      tc_pass_bits(v, p0, p1);
+      const uint32_t sk = skip - t * (uint32_t)kTcTile;  // huge when the skipped sphere is not in this tile
       if (sk < 32u) p0 &= ~(1u << sk);
-      else if (sk < 64u) p1 &= ~(1u << (sk - 32u));
-      const uint32_t ebase = (slot << kGroupBits) + t * 64u;
+      else if (sk < (uint32_t)kTcTile) p1 &= ~(1u << (sk - 32u));
+      const uint32_t ebase = (slot << kGroupBits) + t * (uint32_t)kTcTile;
       append(p0, ebase);
       append(p1, ebase + 32u);
     }
@@ -848,9 +853,9 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
   return wcnt;
 }
 
-// The persistent kernel with the tensor-core filter: ONE CTA of 512 threads (four warpgroups) per
+// The persistent kernel with the tensor-core filter: ONE CTA of kTcBlock threads (five warpgroups) per
 // SM -- the sphere operand (8 KB per 64 spheres) lives once per SM in shared memory and the SM's
-// 512 TMEM columns are split four ways (32 columns of ray features + 64 of accumulators per group).
+// 512 TMEM columns are split between the warpgroups (32 columns of ray features + one accumulator tile each).
 // Shade and resolve are the warp-level phases of fused_kernel, unchanged.
 template <bool SMEM, bool F32HIT>
 __global__ void __launch_bounds__(kTcBlock, 1)
@@ -860,7 +865,7 @@ fused_tc_kernel(const __grid_constant__ WaveParams P) {
   __shared__ __align__(8) uint64_t s_mma[kTcGroups];
   __shared__ uint32_t s_tmem;
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, gid = warp >> 2;
-  const uint32_t op_floats = P.scene.tc_tiles * 4u * 512u;
+  const uint32_t op_floats = P.scene.tc_tiles * 4u * (uint32_t)kTcSlabFloats;
   float *s_op = reinterpret_cast<float *>(smem_raw);
   unsigned char *after_op = smem_raw + (size_t)op_floats * 4u;
   WarpState &W = reinterpret_cast<WarpState *>(after_op)[warp];
@@ -880,7 +885,7 @@ fused_tc_kernel(const __grid_constant__ WaveParams P) {
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_g = s_tmem + gid * 128u;
+  const uint32_t tmem_g = s_tmem + gid * kTcGroupCols;
   const bool issuer = (threadIdx.x & 127u) == 0u;
   const uint32_t npix = P.width * P.height;
   const uint32_t total_items = npix * P.n_orders;  // < 2^32: 2^26 pixels x 64 slices at most
@@ -977,7 +982,7 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
 // one CTA of 512 threads per SM; shared memory = sphere operand | 16 warp states | per-hit rows
 static cudaError_t launch_fused_tc(WaveParams &p, void *pool, uint32_t pool_slots, bool f32hit, int sm_count,
                                    size_t smem_optin_max, bool *in_smem_out, int *grid_out, cudaStream_t st) {
-  const size_t op_bytes = (size_t)p.scene.tc_tiles * 8192u;
+  const size_t op_bytes = (size_t)p.scene.tc_tiles * 4u * (size_t)kTcSlabFloats * 4u;
   const size_t warp_smem = (size_t)kTcWarps * sizeof(WarpState);
   const size_t scene_smem = (size_t)p.scene.n_pad * 56;
   const bool in_smem = op_bytes + warp_smem + scene_smem <= smem_optin_max;
@@ -1009,7 +1014,7 @@ cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float
   if (use_bvh && !p.scene.bvh_nodes) return cudaErrorInvalidValue;
   if (use_bvh && f32_hit) return cudaErrorInvalidValue;
   if (use_tc) {
-    if (use_bvh || !p.scene.tc_op || p.scene.tc_tiles == 0 || p.scene.tc_tiles > kTcMaxTiles) return cudaErrorInvalidValue;
+    if (use_bvh || !p.scene.tc_op || p.scene.tc_tiles == 0 || p.scene.n > kTcMaxSpheres) return cudaErrorInvalidValue;
     bool in_smem = false;
     int grid = 0;
     cudaError_t e = launch_fused_tc(p, pool, pool_slots, f32_hit, sm_count, smem_optin_max, &in_smem, &grid, st);
