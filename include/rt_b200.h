@@ -202,6 +202,21 @@ int rt_primary_hits(const rt_scene *, const rt_camera *, uint32_t width, uint32_
                     int32_t device, int use_f64, int32_t *ids, double *t, double *normal,
                     uint8_t *front_face);
 
+/* --- rt_primary_hits for callers that may not allocate (code under CUDA graph capture, serving
+ *     loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ *     Same kernels, same outputs (HOST arrays) and same results
+ *     as rt_primary_hits, but the device-side result table lives in a static __device__ array of
+ *     RT_STATIC_MAX_PIXELS * 37 bytes (4.6 MiB) that every GPU which loads the library holds until
+ *     the process exits; the call makes no cudaMalloc / cudaFree / cudaMallocHost and creates no
+ *     stream or event.  width * height > RT_STATIC_MAX_PIXELS is rejected with RT_E_INVALID.
+ *     Work is enqueued on `cuda_stream` (a cudaStream_t, NULL = default stream) and the call
+ *     returns after that stream has drained.  All calls share the one array per GPU: the library
+ *     serialises them with a process-wide lock; calls that overlapped on the GPU would race. */
+#define RT_STATIC_MAX_PIXELS 131072u
+int rt_primary_hits_static(const rt_scene *, const rt_camera *, uint32_t width, uint32_t height,
+                           int32_t device, int use_f64, void *cuda_stream, int32_t *ids, double *t,
+                           double *normal, uint8_t *front_face);
+
 /* --- measurement aid: sustained FP32 FFMA throughput of the device (TFLOP/s, FMA = 2),
  *     measured with a register-resident micro-kernel; the roofline denominator of bench.py. */
 int rt_measure_fp32_peak(int32_t device, float *tflops, float *sm_clock_mhz_est);

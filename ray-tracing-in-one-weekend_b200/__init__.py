@@ -66,7 +66,7 @@ SYMBOLS = [
     "rt_frame_set_stream", "rt_measure_fp32_peak", "rt_render_image_multi",
     "rt_scene_update", "rt_frame_stats", "rt_release_cached_frames", "rt_write_pnm",
     "rt_finalize_bands", "rt_finalize_to_file", "rt_multi_create", "rt_multi_set_scene",
-    "rt_multi_render", "rt_multi_destroy", "rt_tc_filter_probe",
+    "rt_multi_render", "rt_multi_destroy", "rt_tc_filter_probe", "rt_primary_hits_static",
 ]
 
 BAND_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint8), C.c_uint32, C.c_uint32)
@@ -384,6 +384,24 @@ def primary_hits(scene: Scene, cam: Camera, width: int, height: int, use_f64: bo
                                  C.c_int32(device), C.c_int(1 if use_f64 else 0),
                                  C.c_void_p(ids.ctypes.data), C.c_void_p(t.ctypes.data),
                                  C.c_void_p(nrm.ctypes.data), C.c_void_p(ff.ctypes.data)))
+    return ids, t, nrm, ff
+
+
+STATIC_MAX_PIXELS = 131072  # RT_STATIC_MAX_PIXELS
+
+
+def primary_hits_static(scene: Scene, cam: Camera, width: int, height: int, use_f64: bool, device=0, stream=0):
+    """primary_hits without any device allocation (rt_primary_hits_static: static scratch of
+    STATIC_MAX_PIXELS pixels per GPU; larger frames raise).  No counterpart in the reference."""
+    ids = np.empty((height, width), np.int32)
+    t = np.empty((height, width), np.float64)
+    nrm = np.empty((height, width, 3), np.float64)
+    ff = np.empty((height, width), np.uint8)
+    cc = cam.c()
+    _check(lib().rt_primary_hits_static(scene._h, C.byref(cc), C.c_uint32(width), C.c_uint32(height),
+                                        C.c_int32(device), C.c_int(1 if use_f64 else 0), C.c_void_p(stream),
+                                        C.c_void_p(ids.ctypes.data), C.c_void_p(t.ctypes.data),
+                                        C.c_void_p(nrm.ctypes.data), C.c_void_p(ff.ctypes.data)))
     return ids, t, nrm, ff
 
 
