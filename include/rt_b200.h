@@ -106,7 +106,13 @@ typedef struct rt_stats {
   uint32_t launches;     /* kernels launched by this call */
   float frame_ms;        /* device time from the start of rt_render to the end of the finalise
                             kernel on the frame's stream (set by rt_finalize) */
+  uint32_t filter_unit;  /* where the brute-force line-sphere filter of the last render ran:
+                            RT_FILTER_SIMT (FFMA2 loop), RT_FILTER_TENSOR (tcgen05 3xTF32
+                            contraction) or RT_FILTER_NONE (BVH traversal / RT_FLAG_NO_FILTER) */
 } rt_stats;
+#define RT_FILTER_NONE 0u
+#define RT_FILTER_SIMT 1u
+#define RT_FILTER_TENSOR 2u
 
 typedef struct rt_scene rt_scene;   /* device-resident flattened hittable_list */
 typedef struct rt_frame rt_frame;   /* device-resident accumulation buffers of one frame */

@@ -55,7 +55,7 @@ class _Config(C.Structure):
 class _Stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays", C.c_uint64), ("sphere_tests", C.c_uint64),
                 ("render_ms", C.c_float), ("finalize_ms", C.c_float), ("launches", C.c_uint32),
-                ("frame_ms", C.c_float)]
+                ("frame_ms", C.c_float), ("filter_unit", C.c_uint32)]
 
 
 # every symbol include/rt_b200.h declares
@@ -139,11 +139,12 @@ class Stats:
     finalize_ms: float = 0.0
     launches: int = 0
     frame_ms: float = 0.0
+    filter_unit: int = 0  # FILTER_NONE / FILTER_SIMT / FILTER_TENSOR
 
     @staticmethod
     def of(s: _Stats) -> "Stats":
         return Stats(s.samples, s.rays, s.sphere_tests, s.render_ms, s.finalize_ms, s.launches,
-                     s.frame_ms)
+                     s.frame_ms, s.filter_unit)
 
 
 def spheres_from_rows(rows: np.ndarray):
@@ -388,6 +389,7 @@ def primary_hits(scene: Scene, cam: Camera, width: int, height: int, use_f64: bo
 
 
 STATIC_MAX_PIXELS = 131072  # RT_STATIC_MAX_PIXELS
+FILTER_NONE, FILTER_SIMT, FILTER_TENSOR = 0, 1, 2  # rt_stats.filter_unit
 
 
 def primary_hits_static(scene: Scene, cam: Camera, width: int, height: int, use_f64: bool, device=0, stream=0):

@@ -455,6 +455,7 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
   }
 
   uint32_t launches = 0;
+  f->last_tc = false; f->last_filter = RT_FILTER_NONE;
   CU(cudaMemsetAsync(f->counters, 0, sizeof(unsigned long long), f->stream));
   CU(cudaMemsetAsync(f->counters + 2, 0, sizeof(unsigned long long), f->stream));
   CU(cudaEventRecord(f->ev[0], f->stream));
@@ -473,6 +474,8 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
                  (cfg->flags & RT_FLAG_F32_HIT) != 0, use_tc, f->sm_count, f->smem_optin, f->stream, &info));
     launches = info.launches;
     f->last_tc = info.tensor_core_filter;
+    f->last_filter = info.tensor_core_filter ? RT_FILTER_TENSOR
+                     : (use_bvh || (cfg->flags & RT_FLAG_NO_FILTER)) ? RT_FILTER_NONE : RT_FILTER_SIMT;
   }
   CU(cudaEventRecord(f->ev[1], f->stream));
   CU(cudaMemcpyAsync(f->host_words + 2, f->counters + 2, sizeof(unsigned long long), cudaMemcpyDeviceToHost, f->stream));
@@ -491,6 +494,7 @@ extern "C" int rt_render(const rt_scene *sc, const rt_camera *cam, const rt_conf
     memset(stats, 0, sizeof *stats);
     stats->samples = f->last_samples;
     stats->launches = f->last_launches;
+    stats->filter_unit = f->last_filter;
   }
   if (caller_stream(f)) return RT_OK;  // asynchronous: timings through rt_frame_stats()
   CU(cudaStreamSynchronize(f->stream));
@@ -609,6 +613,7 @@ extern "C" int rt_frame_stats(rt_frame *f, rt_stats *stats) {
     if (f->host_words[2]) return fail(RT_E_CUDA, "a tensor-core MMA of the filter never completed (bounded wait expired)");
     stats->samples = f->last_samples;
     stats->launches = f->last_launches;
+    stats->filter_unit = f->last_filter;
     CU(cudaEventElapsedTime(&stats->render_ms, f->ev[0], f->ev[1]));
   }
   if (f->finalized) {

@@ -72,6 +72,7 @@ struct rt_frame {
   uint32_t last_launches;
   bool rendered, finalized;
   bool last_tc;             // the last render ran the tensor-core filter
+  uint32_t last_filter;     // RT_FILTER_* of the last render (rt_stats.filter_unit)
   void *pool;               // path-slot pool (allocated on first use)
   uint32_t pool_slots;
   // hand-out order of the next frame: pixels by descending cost of the frame rendered before

@@ -141,6 +141,7 @@ extern "C" int rt_multi_render(rt_multi *m, const rt_camera *cam, const rt_confi
       memset(&sg, 0, sizeof sg);
       CU(cudaEventElapsedTime(&sg.render_ms, fg->ev[0], fg->ev[1]));
       stats->samples += fg->last_samples;
+      stats->filter_unit = fg->last_filter;
       stats->launches += fg->last_launches + 1;
       if (sg.render_ms > stats->render_ms) stats->render_ms = sg.render_ms;
     }

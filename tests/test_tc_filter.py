@@ -23,6 +23,9 @@ def test_tensor_core_and_simt_filters_render_the_same_bytes(rt, name, W, H, spp,
     assert a[2].rays == b[2].rays and a[2].samples == b[2].samples
     assert np.array_equal(a[1], b[1]) and np.array_equal(a[0], b[0])
     assert a[1].max() > 0
+    # rt_stats says which unit ran the filter (bench.py's roofline line quotes it)
+    assert a[2].filter_unit == (rt.FILTER_TENSOR if len(rows) >= 32 else rt.FILTER_SIMT)
+    assert b[2].filter_unit == rt.FILTER_SIMT
 
 
 def test_scenes_beyond_the_operand_limit_take_the_simt_loop(rt):
@@ -36,6 +39,7 @@ def test_scenes_beyond_the_operand_limit_take_the_simt_loop(rt):
     a = rt.render_image(rt.Scene(big), cam, rt.Config(W, H, 4, 50, seed=2))
     b = rt.render_image(rt.Scene(big), cam, rt.Config(W, H, 4, 50, seed=2, flags=rt.FLAG_BVH))
     assert np.array_equal(a[1], b[1])
+    assert a[2].filter_unit == rt.FILTER_SIMT and b[2].filter_unit == rt.FILTER_NONE
 
 
 def probe_rays(rows, n, seed):
