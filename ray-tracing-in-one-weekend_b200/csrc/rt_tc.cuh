@@ -89,6 +89,11 @@ __device__ __forceinline__ void tc_pass_bits(const uint32_t (&v)[kTcTile], uint3
   p1 = kTcTile == 64 ? ~tc_sign_mask<4>(v, 32) : (~tc_sign_mask<2>(v, 32) & 0xffffu);
 }
 
+__device__ __forceinline__ uint32_t tc_pass_bits_lo(const uint32_t (&v)[kTcTile]) { return ~tc_sign_mask<4>(v, 0); }
+__device__ __forceinline__ uint32_t tc_pass_bits_hi(const uint32_t (&v)[kTcTile]) {
+  return kTcTile == 64 ? ~tc_sign_mask<4>(v, 32) : (~tc_sign_mask<2>(v, 32) & 0xffffu);
+}
+
 // psi(o, d) -> the ray's 32 K slots {hi, lo, hi} x 9, k (hi, lo), 1, 1, 0
 __device__ __forceinline__ void tc_ray_slots(const float4 o, const float4 d, uint32_t (&slot)[kTcK]) {
   const float od = o.x * d.x + o.y * d.y + o.z * d.z;
@@ -147,6 +152,13 @@ __device__ __forceinline__ void tc_ray_slots(const float4 o, const float4 d, uin
                  "=r"(v[o + 15])                                                                            \
                : "r"(addr)                                                                                  \
                : "memory")
+
+// columns 32 .. kTcTile-1 of this thread's row
+#define TC_LD_TILE_HI(addr, v)                                   \
+  do {                                                           \
+    if (kTcTile == 64) { TC_LD32((addr) + 32u, v, 32); }         \
+    else { TC_LD16((addr) + 32u, v, 32); }                       \
+  } while (0)
 
 // this thread's row of an accumulator tile -> registers
 #define TC_LD_TILE(addr, v)                                      \

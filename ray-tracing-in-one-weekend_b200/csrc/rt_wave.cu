@@ -48,7 +48,9 @@ struct __align__(16) WarpState {
   float4 rd[64];               // {unit direction, index of the sphere the ray just left (int bits) or -1}
   unsigned long long key[64];  // root numerator of the closest hit so far (bits of a positive double)
   int id[64];                  // its sphere, -1 = none
-  uint32_t list[kListSmem];    // {slot << kGroupBits | decision group}, ascending groups
+  uint32_t list[kListSmem];    // {slot << kGroupBits | decision group}; the resolve does not depend on the order
+  uint32_t cnt;                // entries appended by the tensor-core filter (lanes claim ranges with one atomic)
+  uint32_t pad_[3];
 };
 
 // @phase helpers
@@ -762,6 +764,7 @@ fused_kernel(const __grid_constant__ WaveParams P, const __grid_constant__ Const
 #ifndef RTW_TC_BLOCK
 #define RTW_TC_BLOCK 640
 #endif
+
 constexpr int kTcBlock = RTW_TC_BLOCK, kTcWarps = kTcBlock / 32, kTcGroups = kTcBlock / 128;
 constexpr uint32_t kTcGroupCols = 32u + (uint32_t)kTcTile;  // TMEM columns of a warpgroup: ray features + one accumulator tile
 static_assert(kTcGroups * kTcGroupCols <= 512u, "the warpgroups' tensor-memory shares exceed the SM's 512 columns");
@@ -786,29 +789,28 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
   const uint32_t tiles = P.scene.tc_tiles;
   const uint32_t lane_base = (((threadIdx.x >> 5) & 3u) * 32u) << 16;
   const uint32_t a_tmem = tmem_g, d_tmem = tmem_g + 32u;
-  const uint32_t lt = (1u << lane) - 1u;
   constexpr uint32_t gcap = 64u * kListGlobalPerSlot;
-  uint32_t wcnt = 0;  // entries recorded so far (warp-uniform)
-  // candidates of one 32-sphere half of a tile -> the warp's list, one ballot round per set bit
-  auto append = [&](uint32_t p, const uint32_t ebase) {
-    while (__any_sync(FULL, p != 0u)) {
-      const bool has = p != 0u;
-      const uint32_t b = (uint32_t)__ffs((int)p) - 1u;
-      p &= p - 1u;
-      const unsigned bal = __ballot_sync(FULL, has);
-      const uint32_t pos = wcnt + __popc(bal & lt);
-      if (has) {
-        if (pos < kListSmem) W.list[pos] = ebase + b;
-        else if (pos - kListSmem < gcap) glist[pos - kListSmem] = ebase + b;
-      }
-      wcnt += __popc(bal);
+  // the elected thread starts the four K steps of tile `t` (descriptors of consecutive K slabs are
+  // kTcSlabUnits apart in the address field) and commits them to the group's mbarrier
+  auto issue = [&](const uint32_t t) {
+    if (issuer) {
+      tc_fence_after();
+      const uint64_t dt = desc0 + (uint64_t)(t * 4u) * (uint64_t)kTcSlabUnits;
+#pragma unroll
+      for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * (uint64_t)kTcSlabUnits, kTcIdesc, j);
+      tc_commit(bar);
     }
   };
+  if (lane == 0) W.cnt = 0u;  // ordered before the first append by the group barriers below
 #pragma unroll 1
   for (uint32_t blk = 0; blk < 2u; ++blk) {
     const uint32_t slot = lane + 32u * blk;
     const float4 o = W.ro[slot], d = W.rd[slot];
-    const uint32_t skip = (uint32_t)__float_as_int(d.w);  // the sphere the ray just left, or -1
+    // the sphere the ray just left (or -1) never passes: its tile and the two words that clear its bit
+    const uint32_t skip = (uint32_t)__float_as_int(d.w);
+    const uint32_t skip_t = skip / (uint32_t)kTcTile, skip_b = skip - skip_t * (uint32_t)kTcTile;
+    const uint32_t keep0 = skip_b < 32u ? ~(1u << skip_b) : ~0u;
+    const uint32_t keep1 = skip_b < 32u ? ~0u : ~(1u << (skip_b - 32u));
     {
       uint32_t sv[kTcK];
       tc_ray_slots(o, d, sv);
@@ -817,16 +819,9 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     tc_fence_before();
     group_sync(gid);  // the 128 rays' features are in tensor memory
+    issue(0u);
 #pragma unroll 1
     for (uint32_t t = 0; t < tiles; ++t) {
-      if (issuer) {
-        tc_fence_after();
-        // descriptors of the tile's four K slabs: consecutive slabs = + kTcSlabUnits in the address field
-        const uint64_t dt = desc0 + (uint64_t)(t * 4u) * (uint64_t)kTcSlabUnits;
-#pragma unroll
-        for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * (uint64_t)kTcSlabUnits, kTcIdesc, j);
-        tc_commit(bar);
-      }
       // bounded wait: a tensor-core fault must not hang the GPU; after one expiry (bit 31) the thread
       // stops waiting, the frame finishes with garbage and the host reports the status word
       if (!(parity & 0x80000000u) && !mbar_wait_bounded(bar, parity & 1u)) {
@@ -836,21 +831,38 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
       parity ^= 1u;
       tc_fence_after();
       uint32_t v[kTcTile];
-      TC_LD_TILE(d_tmem + lane_base, v);
+      uint32_t p0, p1;
+      // the row comes back in two halves: the sign bits of the first are folded while the second is in flight
+      TC_LD32(d_tmem + lane_base, v, 0);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      TC_LD_TILE_HI(d_tmem + lane_base, v);
+      p0 = tc_pass_bits_lo(v);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       tc_fence_before();
-      group_sync(gid);  // D is free: the next tile's MMAs overlap the work below
-      uint32_t p0, p1;
-      tc_pass_bits(v, p0, p1);
-      const uint32_t sk = skip - t * (uint32_t)kTcTile;  // huge when the skipped sphere is not in this tile
-      if (sk < 32u) p0 &= ~(1u << sk);
-      else if (sk < (uint32_t)kTcTile) p1 &= ~(1u << (sk - 32u));
+      group_sync(gid);  // D is free: the next tile's MMAs run under the mask and append work below
+      if (t + 1u < tiles) issue(t + 1u);
+      p1 = tc_pass_bits_hi(v);
+      if (t == skip_t) { p0 &= keep0; p1 &= keep1; }
       const uint32_t ebase = (slot << kGroupBits) + t * (uint32_t)kTcTile;
-      append(p0, ebase);
-      append(p1, ebase + 32u);
+      // candidates -> the warp's list: the lane claims a range with one shared-memory atomic
+      if ((p0 | p1) != 0u) {
+        uint32_t pos = atomicAdd(&W.cnt, (uint32_t)(__popc(p0) + __popc(p1)));
+        auto put = [&](uint32_t p, const uint32_t eb) {
+          while (p != 0u) {
+            const uint32_t e = eb + (uint32_t)__ffs((int)p) - 1u;
+            p &= p - 1u;
+            if (pos < kListSmem) W.list[pos] = e;
+            else if (pos - kListSmem < gcap) glist[pos - kListSmem] = e;
+            ++pos;
+          }
+        };
+        put(p0, ebase);
+        put(p1, ebase + 32u);
+      }
     }
   }
-  return wcnt;
+  __syncwarp();
+  return W.cnt;
 }
 
 // The persistent kernel with the tensor-core filter: ONE CTA of kTcBlock threads (five warpgroups) per
@@ -979,7 +991,7 @@ static cudaError_t launch_fused_t(WaveParams &p, void *pool, uint32_t pool_slots
   return cudaGetLastError();
 }
 
-// one CTA of 512 threads per SM; shared memory = sphere operand | 16 warp states | per-hit rows
+// one CTA of kTcBlock threads per SM; shared memory = sphere operand | warp states | per-hit rows
 static cudaError_t launch_fused_tc(WaveParams &p, void *pool, uint32_t pool_slots, bool f32hit, int sm_count,
                                    size_t smem_optin_max, bool *in_smem_out, int *grid_out, cudaStream_t st) {
   const size_t op_bytes = (size_t)p.scene.tc_tiles * 4u * (size_t)kTcSlabFloats * 4u;
