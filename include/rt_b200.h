@@ -91,7 +91,7 @@ typedef struct rt_config {
                                  book's first diffuse steps (archive/listing30/color.h:8-17, before listing35;
                                  archive-gpu/image7...11/color.h) */
 #define RT_FLAG_SIMT_FILTER 256u /* brute-force scan with the FFMA2 filter loop (CUDA cores) even where the
-                                 tensor-core form applies.  By default scenes of up to 1024 spheres run the
+                                 tensor-core form applies.  By default scenes of 32 to 960 spheres run the
                                  filter as one tf32 contraction on the tensor cores (tcgen05);
                                  both find every true hit, so the image is byte-identical either way. */
 #define RT_FLAG_ALL (RT_FLAG_COUNT_RAYS | RT_FLAG_BVH | RT_FLAG_V4_MODEL | RT_FLAG_F32_HIT | RT_FLAG_NO_FILTER | \
@@ -229,7 +229,7 @@ int rt_measure_fp32_peak(int32_t device, float *tflops, float *sm_clock_mhz_est)
 
 /* --- measurement / validation aid: the brute-force filter written as ONE tf32 contraction on the
  *     tensor cores (tcgen05.mma, accumulators in tensor memory) on `n` rays
- *     {ox, oy, oz, |d| > 0}, {unit d, -} against a scene of up to 1024 spheres.  masks: HOST
+ *     {ox, oy, oz, |d| > 0}, {unit d, -} against a scene of up to 960 spheres.  masks: HOST
  *     [n][tiles] 64-bit words, bit b of word t set = sphere tile_spheres * t + b passes; values
  *     (optional): HOST [n_values][tiles][tile_spheres] raw filter values; ms: device time of
  *     `repeats` passes over the rays.  Not part of the render path. */

@@ -1,5 +1,5 @@
 """The brute-force filter on the tensor cores (csrc/rt_tc.cu, fused_tc_kernel in csrc/rt_wave.cu):
-scenes of up to 1024 spheres run `every ray against every sphere` (src/cpu/hittable_list.h:28-43) as
+scenes of 32 to 960 spheres run `every ray against every sphere` (src/cpu/hittable_list.h:28-43) as
 one 3xTF32 contraction with tcgen05.mma.  It only has to be CONSERVATIVE (never drop a line-sphere
 pass); the f64 resolve behind it decides like the reference.  So: (1) images, linear sums and ray
 counts are byte-identical to the FFMA2 filter loop (RT_FLAG_SIMT_FILTER) in every model; (2) the
@@ -29,7 +29,7 @@ def test_tensor_core_and_simt_filters_render_the_same_bytes(rt, name, W, H, spp,
 
 
 def test_scenes_beyond_the_operand_limit_take_the_simt_loop(rt):
-    """1025+ spheres: the sphere operand no longer fits a CTA's shared memory; the render still works
+    """more than 960 spheres: the sphere operand no longer fits a CTA's shared memory; the render still works
     (FFMA2 loop) and equals the BVH image."""
     cover = golden("cover_small.npz")["spheres"]
     big = np.concatenate([cover] + [cover[1:] + np.array([0, 0, 30.0 * k, 0, 0, 0, 0, 0, 0]) for k in (1, 2)])
