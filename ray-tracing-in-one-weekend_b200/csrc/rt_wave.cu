@@ -842,14 +842,6 @@ __device__ __forceinline__ uint32_t filter_rays_tc(const WaveParams &P, WarpStat
       group_sync(gid);  // D is free: the next tile's MMAs run under the mask and append work below
       if (t + 1u < tiles) issue(t + 1u);
       p1 = tc_pass_bits_hi(v);
-#ifdef RTW_TC_DBG_DOUBLE_SHF
-      {
-#pragma unroll
-        for (int i = 0; i < (int)kTcTile; ++i) asm volatile("" : "+r"(v[i]));
-        p0 &= tc_pass_bits_lo(v);
-        p1 &= tc_pass_bits_hi(v);
-      }
-#endif
       if (t == skip_t) { p0 &= keep0; p1 &= keep1; }
       const uint32_t ebase = (slot << kGroupBits) + t * (uint32_t)kTcTile;
       // candidates -> the warp's list: the lane claims a range with one shared-memory atomic
