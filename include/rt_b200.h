@@ -91,7 +91,7 @@ typedef struct rt_config {
                                  book's first diffuse steps (archive/listing30/color.h:8-17, before listing35;
                                  archive-gpu/image7...11/color.h) */
 #define RT_FLAG_SIMT_FILTER 256u /* brute-force scan with the FFMA2 filter loop (CUDA cores) even where the
-                                 tensor-core form applies.  By default scenes of 32 to 960 spheres run the
+                                 tensor-core form applies.  By default scenes of 32 spheres and more run the
                                  filter as one tf32 contraction on the tensor cores (tcgen05);
                                  both find every true hit, so the image is byte-identical either way. */
 #define RT_FLAG_ALL (RT_FLAG_COUNT_RAYS | RT_FLAG_BVH | RT_FLAG_V4_MODEL | RT_FLAG_F32_HIT | RT_FLAG_NO_FILTER | \

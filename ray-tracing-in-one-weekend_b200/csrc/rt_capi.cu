@@ -43,6 +43,7 @@ const EnvCfg &env_cfg() {
     EnvCfg c;
     const char *e;
     c.no_tc = getenv("RT_B200_NO_TC") != nullptr;
+    c.no_tc_stream = getenv("RT_B200_NO_TC_STREAM") != nullptr;
     c.no_const_rows = getenv("RT_B200_NO_CONST_ROWS") != nullptr;
     c.no_cost_order = getenv("RT_B200_NO_COST_ORDER") != nullptr;
     e = getenv("RT_B200_HEAVY_QUARTER_RAYS");
@@ -412,10 +413,11 @@ int rt_render_enqueue(const rt_scene *sc, const rt_camera *cam, const rt_config 
   // an empty world has no hierarchy to walk (its root box would be degenerate): brute force
   const bool use_bvh = (cfg->flags & RT_FLAG_BVH) != 0 && sc->n > 0;
   if (use_bvh && (rc = rt_scene_ensure_bvh(sc)) != RT_OK) return rc;
-  // the brute-force filter runs on the tensor cores when the sphere operand fits one CTA's shared
-  // memory (32 to 1024 spheres); RT_FLAG_SIMT_FILTER / RT_B200_NO_TC keep the FFMA2 loop
-  // (a handful of spheres is a single trip of the FFMA2 loop: not worth a tensor-core round trip)
-  const bool use_tc = !use_bvh && sc->n >= 32u && sc->n <= kTcMaxSpheres &&
+  // the brute-force filter runs on the tensor cores from 32 spheres up (a handful of spheres is a single
+  // trip of the FFMA2 loop: not worth a tensor-core round trip): the sphere operand resident in shared
+  // memory up to kTcMaxSpheres, streamed through it in chunks beyond; RT_FLAG_SIMT_FILTER / RT_B200_NO_TC
+  // keep the FFMA2 loop, RT_B200_NO_TC_STREAM keeps it for the scenes that would stream
+  const bool use_tc = !use_bvh && sc->n >= 32u && (sc->n <= kTcMaxSpheres || !env_cfg().no_tc_stream) &&
                       !(cfg->flags & (RT_FLAG_NO_FILTER | RT_FLAG_SIMT_FILTER)) && !env_cfg().no_tc;
   if (use_tc && (rc = rt_scene_ensure_tc(sc)) != RT_OK) return rc;
   CamFrame cf;

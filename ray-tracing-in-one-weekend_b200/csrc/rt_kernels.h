@@ -71,6 +71,7 @@ struct WaveParams {
 // RT_B200_* experiment switches, read ONCE per process.
 struct EnvCfg {
   bool no_tc;               // RT_B200_NO_TC: SIMT filter loop even where the tensor-core filter applies
+  bool no_tc_stream;        // RT_B200_NO_TC_STREAM: ... for scenes beyond kTcMaxSpheres only
   bool no_const_rows;       // RT_B200_NO_CONST_ROWS
   bool no_cost_order;       // RT_B200_NO_COST_ORDER
   int heavy_quarter_rays;   // RT_B200_HEAVY_QUARTER_RAYS, -1 unset

@@ -935,6 +935,176 @@ fused_tc_kernel(const __grid_constant__ WaveParams P) {
   if (warp == 0) tmem_dealloc(s_tmem, 512);
 }
 
+// ================================================================ tensor-core filter, streamed operand
+// Scenes beyond kTcMaxSpheres: the sphere operand (128 B per sphere) no longer fits a CTA's shared memory, so
+// it streams through two chunk buffers with bulk (TMA) copies.  All five warpgroups of the CTA have to look
+// at the same chunk, so the CTA runs its waves in step: shade (CTA-wide exit vote), then per ray block the
+// chunks in order -- wait for the chunk's bytes, rounds of filter_rays_tc over its tiles, a CTA barrier, and
+// one thread starts the copy of the chunk after next into the buffer just freed -- then resolve.
+#ifndef RTW_TCS_CHUNK_TILES
+#define RTW_TCS_CHUNK_TILES 6
+#endif
+constexpr uint32_t kTcsChunkTiles = RTW_TCS_CHUNK_TILES;
+constexpr uint32_t kTcsTileBytes = 4u * (uint32_t)kTcSlabFloats * 4u;  // 8 KB per 64 spheres
+constexpr uint32_t kTcsChunkBytes = kTcsChunkTiles * kTcsTileBytes;
+
+__device__ __forceinline__ uint32_t filter_rays_tc_stream(const WaveParams &P, WarpState &W, uint32_t *glist,
+                                                          const uint32_t lane, const uint32_t gid, const bool issuer,
+                                                          uint64_t *bar, uint32_t &parity, const uint32_t tmem_g,
+                                                          unsigned char *bufs, uint64_t *full, uint32_t &fpar) {
+  const uint32_t tiles = P.scene.tc_tiles;
+  const uint32_t nchunks = (tiles + kTcsChunkTiles - 1u) / kTcsChunkTiles, visits = 2u * nchunks;
+  const uint32_t lane_base = (((threadIdx.x >> 5) & 3u) * 32u) << 16;
+  const uint32_t a_tmem = tmem_g, d_tmem = tmem_g + 32u;
+  constexpr uint32_t gcap = 64u * kListGlobalPerSlot;
+  const bool producer = threadIdx.x == 0u;
+  // chunk of visit v (the chunks of ray block 0, then the same chunks again for block 1) -> buffer v & 1
+  auto load = [&](const uint32_t v) {
+    const uint32_t c = v < nchunks ? v : v - nchunks, b = v & 1u;
+    const uint32_t t0 = c * kTcsChunkTiles, nt = min(kTcsChunkTiles, tiles - t0), bytes = nt * kTcsTileBytes;
+    mbar_expect_tx(full + b, bytes);
+    bulk_g2s(bufs + (size_t)b * kTcsChunkBytes,
+             reinterpret_cast<const unsigned char *>(P.scene.tc_op) + (size_t)t0 * kTcsTileBytes, bytes, full + b);
+  };
+  // every warp of the CTA is past the barrier that ended the previous wave's last chunk: both buffers are free
+  if (producer) { load(0u); if (visits > 1u) load(1u); }
+  if (lane == 0) W.cnt = 0u;  // ordered before the first append by the group barriers below
+  uint32_t slot = lane, skip_t = 0u, keep0 = ~0u, keep1 = ~0u;
+#pragma unroll 1
+  for (uint32_t v = 0; v < visits; ++v) {
+    const uint32_t blk = v >= nchunks ? 1u : 0u, c = v - blk * nchunks, b = v & 1u;
+    if (c == 0u) {
+      // a new block of rays: features -> tensor memory (the MMAs of the block before are complete)
+      slot = lane + 32u * blk;
+      const float4 o = W.ro[slot], d = W.rd[slot];
+      const uint32_t skip = (uint32_t)__float_as_int(d.w);
+      skip_t = skip / (uint32_t)kTcTile;
+      const uint32_t skip_b = skip - skip_t * (uint32_t)kTcTile;
+      keep0 = skip_b < 32u ? ~(1u << skip_b) : ~0u;
+      keep1 = skip_b < 32u ? ~0u : ~(1u << (skip_b - 32u));
+      uint32_t sv[kTcK];
+      tc_ray_slots(o, d, sv);
+      TC_ST32(a_tmem + lane_base, sv);
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      group_sync(gid);
+    }
+    // the chunk's bytes have landed (bulk copy -> mbarrier); parity bit b of fpar is buffer b's phase
+    mbar_wait(full + b, (fpar >> b) & 1u);
+    fpar ^= 1u << b;
+    const uint32_t t0 = c * kTcsChunkTiles, nt = min(kTcsChunkTiles, tiles - t0);
+    const uint64_t desc0 = tc_smem_desc(bufs + (size_t)b * kTcsChunkBytes);
+    auto issue = [&](const uint32_t t) {
+      if (issuer) {
+        tc_fence_after();
+        const uint64_t dt = desc0 + (uint64_t)(t * 4u) * (uint64_t)kTcSlabUnits;
+#pragma unroll
+        for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * (uint64_t)kTcSlabUnits, kTcIdesc, j);
+        tc_commit(bar);
+      }
+    };
+    issue(0u);
+#pragma unroll 1
+    for (uint32_t t = 0; t < nt; ++t) {
+      if (!(parity & 0x80000000u) && !mbar_wait_bounded(bar, parity & 1u)) {
+        atomicExch(P.status, 1u);
+        parity |= 0x80000000u;
+      }
+      parity ^= 1u;
+      tc_fence_after();
+      uint32_t vv[kTcTile];
+      uint32_t p0, p1;
+      TC_LD32(d_tmem + lane_base, vv, 0);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      TC_LD_TILE_HI(d_tmem + lane_base, vv);
+      p0 = tc_pass_bits_lo(vv);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      group_sync(gid);
+      if (t + 1u < nt) issue(t + 1u);
+      p1 = tc_pass_bits_hi(vv);
+      const uint32_t tg = t0 + t;  // tile of the scene
+      if (tg == skip_t) { p0 &= keep0; p1 &= keep1; }
+      const uint32_t ebase = (slot << kGroupBits) + tg * (uint32_t)kTcTile;
+      if ((p0 | p1) != 0u) {
+        uint32_t pos = atomicAdd(&W.cnt, (uint32_t)(__popc(p0) + __popc(p1)));
+        auto put = [&](uint32_t p, const uint32_t eb) {
+          while (p != 0u) {
+            const uint32_t e = eb + (uint32_t)__ffs((int)p) - 1u;
+            p &= p - 1u;
+            if (pos < kListSmem) W.list[pos] = e;
+            else if (pos - kListSmem < gcap) glist[pos - kListSmem] = e;
+            ++pos;
+          }
+        };
+        put(p0, ebase);
+        put(p1, ebase + 32u);
+      }
+    }
+    // every warpgroup has waited for its last MMA on this buffer: it may be refilled
+    __syncthreads();
+    if (producer && v + 2u < visits) load(v + 2u);
+  }
+  __syncwarp();
+  return W.cnt;
+}
+
+template <bool F32HIT>
+__global__ void __launch_bounds__(kTcBlock, 1)
+fused_tcs_kernel(const __grid_constant__ WaveParams P) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t s_mma[kTcGroups];
+  __shared__ __align__(8) uint64_t s_full[2];
+  __shared__ uint32_t s_tmem;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, gid = warp >> 2;
+  WarpState &W = reinterpret_cast<WarpState *>(smem_raw + 2u * kTcsChunkBytes)[warp];
+  if (threadIdx.x < kTcGroups) mbar_init(&s_mma[threadIdx.x], 1);
+  if (threadIdx.x < 2u) mbar_init(&s_full[threadIdx.x], 1);
+  if (warp == 0) tmem_alloc(&s_tmem, 512);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the barriers are seen by the bulk copies
+  const double4 *exact = P.scene.exact;
+  const float4 *mat = P.scene.mat;
+  const float2 *aux = P.scene.aux;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_g = s_tmem + gid * kTcGroupCols;
+  const bool issuer = (threadIdx.x & 127u) == 0u;
+  const uint32_t npix = P.width * P.height;
+  const uint32_t total_items = npix * P.n_orders;
+  const uint32_t stride = P.n_slots / 2u;
+  const uint32_t base = blockIdx.x * kTcBlock + threadIdx.x;
+  uint32_t *glist = P.glist + (size_t)(blockIdx.x * kTcWarps + warp) * (64u * kListGlobalPerSlot);
+#pragma unroll 1
+  for (int r = 0; r < 2; ++r) {
+    const uint32_t i = base + r * stride, slot = lane + 32u * r;
+    P.thr[i] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+    P.acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    P.it[i] = make_uint4(kNoItem, 0u, 0u, 0u);
+    W.ro[slot] = make_float4(0.f, 0.f, 0.f, -1.f);
+    W.rd[slot] = make_float4(0.f, 1.f, 0.f, __int_as_float(-1));
+    W.key[slot] = kInfKey;
+    W.id[slot] = -1;
+  }
+  uint32_t parity = 0, fpar = 0;
+  for (;;) {
+    uint32_t live = 0;
+#pragma unroll 1
+    for (int r = 0; r < 2; ++r)
+      live += shade_slot<F32HIT>(P, W, lane + 32u * r, base + r * stride, exact, mat, aux, npix, total_items);
+    if (!__syncthreads_or((int)(live != 0u))) break;  // the CTA's waves run in step: it leaves as one
+    const uint32_t n_entries = filter_rays_tc_stream(P, W, glist, lane, gid, issuer, &s_mma[gid], parity, tmem_g,
+                                                     smem_raw, s_full, fpar);
+    __syncwarp();
+    if (n_entries <= kListSmem + 64u * kListGlobalPerSlot) resolve_entries<RTW_G, F32HIT, true>(P, W, glist, n_entries, exact, lane);
+    else resolve_scan<F32HIT>(P, W, exact, lane);
+    __syncwarp();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(s_tmem, 512);
+}
+
 // ================================================================ host side
 size_t wave_pool_bytes(uint32_t n_slots) {
   // thr, acc (float4) + it (uint4) + the candidate entries beyond the shared-memory lists
@@ -1020,16 +1190,41 @@ static cudaError_t launch_fused_tc(WaveParams &p, void *pool, uint32_t pool_slot
   return cudaGetLastError();
 }
 
+// streamed form: two chunk buffers | warp states (the per-hit rows stay in L1/L2)
+static cudaError_t launch_fused_tcs(WaveParams &p, void *pool, uint32_t pool_slots, bool f32hit, int sm_count,
+                                    size_t smem_optin_max, int *grid_out, cudaStream_t st) {
+  const size_t smem = 2u * (size_t)kTcsChunkBytes + (size_t)kTcWarps * sizeof(WarpState);
+  if (smem > smem_optin_max) return cudaErrorInvalidValue;
+  const int grid = sm_count;
+  const uint32_t n_slots = (uint32_t)grid * kTcBlock * 2u;
+  if (n_slots > pool_slots) return cudaErrorInvalidValue;
+  wave_carve(p, pool, n_slots);
+  *grid_out = grid;
+  cudaError_t e;
+  if (f32hit) {
+    auto k = fused_tcs_kernel<true>;
+    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    k<<<grid, kTcBlock, smem, st>>>(p);
+  } else {
+    auto k = fused_tcs_kernel<false>;
+    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    k<<<grid, kTcBlock, smem, st>>>(p);
+  }
+  return cudaGetLastError();
+}
+
 cudaError_t run_fused(WaveParams p, void *pool, uint32_t pool_slots, const float4 *host_rows,
                       bool use_bvh, bool f32_hit, bool use_tc, int sm_count, size_t smem_optin_max,
                       cudaStream_t st, WaveRunInfo *info) {
   if (use_bvh && !p.scene.bvh_nodes) return cudaErrorInvalidValue;
   if (use_bvh && f32_hit) return cudaErrorInvalidValue;
   if (use_tc) {
-    if (use_bvh || !p.scene.tc_op || p.scene.tc_tiles == 0 || p.scene.n > kTcMaxSpheres) return cudaErrorInvalidValue;
+    if (use_bvh || !p.scene.tc_op || p.scene.tc_tiles == 0) return cudaErrorInvalidValue;
     bool in_smem = false;
     int grid = 0;
-    cudaError_t e = launch_fused_tc(p, pool, pool_slots, f32_hit, sm_count, smem_optin_max, &in_smem, &grid, st);
+    cudaError_t e = p.scene.n > kTcMaxSpheres
+                        ? launch_fused_tcs(p, pool, pool_slots, f32_hit, sm_count, smem_optin_max, &grid, st)
+                        : launch_fused_tc(p, pool, pool_slots, f32_hit, sm_count, smem_optin_max, &in_smem, &grid, st);
     if (info) {
       info->launches = 1; info->n_slots = p.n_slots; info->rays_per_lane = 2; info->grid = grid;
       info->rows_in_constant_bank = false; info->scene_in_smem = in_smem; info->tensor_core_filter = true;

@@ -28,18 +28,21 @@ def test_tensor_core_and_simt_filters_render_the_same_bytes(rt, name, W, H, spp,
     assert b[2].filter_unit == rt.FILTER_SIMT
 
 
-def test_scenes_beyond_the_operand_limit_take_the_simt_loop(rt):
-    """more than 960 spheres: the sphere operand no longer fits a CTA's shared memory; the render still works
-    (FFMA2 loop) and equals the BVH image."""
+@pytest.mark.parametrize("copies", [3, 6])
+def test_scenes_beyond_the_operand_limit_stream_it_through_shared_memory(rt, copies):
+    """more than 960 spheres: the sphere operand no longer fits a CTA's shared memory and streams through
+    two chunk buffers (fused_tcs_kernel); same bytes as the FFMA2 loop and as the BVH."""
     cover = golden("cover_small.npz")["spheres"]
-    big = np.concatenate([cover] + [cover[1:] + np.array([0, 0, 30.0 * k, 0, 0, 0, 0, 0, 0]) for k in (1, 2)])
-    assert len(big) > 1024
+    big = np.concatenate([cover] + [cover[1:] + np.array([0, 0, 30.0 * k, 0, 0, 0, 0, 0, 0]) for k in range(1, copies)])
+    assert len(big) > 960
     W, H = 96, 54
     cam = cam_for(rt, "cover", W, H)
     a = rt.render_image(rt.Scene(big), cam, rt.Config(W, H, 4, 50, seed=2))
+    s = rt.render_image(rt.Scene(big), cam, rt.Config(W, H, 4, 50, seed=2, flags=rt.FLAG_SIMT_FILTER))
     b = rt.render_image(rt.Scene(big), cam, rt.Config(W, H, 4, 50, seed=2, flags=rt.FLAG_BVH))
-    assert np.array_equal(a[1], b[1])
-    assert a[2].filter_unit == rt.FILTER_SIMT and b[2].filter_unit == rt.FILTER_NONE
+    assert np.array_equal(a[1], s[1]) and np.array_equal(a[1], b[1]) and np.array_equal(a[0], b[0])
+    assert a[2].rays == s[2].rays == b[2].rays
+    assert a[2].filter_unit == rt.FILTER_TENSOR and s[2].filter_unit == rt.FILTER_SIMT and b[2].filter_unit == rt.FILTER_NONE
 
 
 def probe_rays(rows, n, seed):
