@@ -60,3 +60,41 @@ def test_far_camera(rt, dist):
                     aspect_ratio=96 / 54, aperture=0.0, focus_dist=dist)
     a = identical(rt, rows, cam, 96, 54, 8)
     assert a[2].rays > 1.5 * a[2].samples  # the spheres are really in view
+
+
+def soup(seed, n, spread, rmin, rmax, offset=(0.0, 0.0, 0.0)):
+    """random spheres of all three materials around `offset` (some hollow, some overlapping) on a big ground"""
+    rng = np.random.default_rng(seed)
+    rows = np.zeros((n + 1, 9))
+    off = np.asarray(offset)
+    rows[0] = [off[0], off[1] - 1000.0 - spread, off[2], 1000.0, 0, 0.5, 0.5, 0.5, 0.0]
+    c = rng.uniform(-spread, spread, (n, 3)) + off
+    r = np.exp(rng.uniform(np.log(rmin), np.log(rmax), n))
+    kind = rng.integers(0, 3, n)
+    r = np.where((kind == 2) & (rng.random(n) < 0.3), -0.9 * r, r)  # hollow bubbles
+    rows[1:, :3] = c; rows[1:, 3] = r; rows[1:, 4] = kind
+    rows[1:, 5:8] = rng.uniform(0.2, 1.0, (n, 3))
+    rows[1:, 8] = np.where(kind == 2, 1.5, rng.uniform(0.0, 0.5, n))
+    return rows
+
+
+@pytest.mark.parametrize("seed,n,spread,rmin,rmax,offset", [
+    (1, 200, 4.0, 0.05, 1.0, (0, 0, 0)),          # dense soup, many overlaps, rays start inside spheres
+    (2, 700, 30.0, 0.01, 3.0, (0, 0, 0)),         # radii over 2.5 decades
+    (3, 500, 5.0, 0.002, 0.05, (0, 0, 0)),        # tiny spheres: r^2 down to 4e-6 against |c|^2 ~ 50
+    (4, 300, 5.0, 0.1, 1.0, (3000.0, -2000.0, 1500.0)),  # everything far from the origin: |c|^2 ~ 1.5e7
+    (5, 1500, 20.0, 0.05, 1.5, (0, 0, 0)),        # beyond 960 spheres: streamed operand
+])
+def test_random_soups_both_filters(rt, seed, n, spread, rmin, rmax, offset):
+    """Random geometry the reference scenes never show.  The tensor-core filter (default) and the FFMA2 loop
+    must each render the bytes of the unfiltered f64 scan."""
+    rows = soup(seed, n, spread, rmin, rmax, offset)
+    off = np.asarray(offset, float)
+    W, H = 80, 45
+    cam = rt.Camera(lookfrom=tuple(off + np.array([2.5 * spread, 0.6 * spread, 1.5 * spread])), lookat=tuple(off),
+                    vfov=35.0, aspect_ratio=W / H, aperture=0.02 * spread, focus_dist=3.0 * spread)
+    a = identical(rt, rows, cam, W, H, 6, seed=seed)
+    assert a[2].filter_unit == rt.FILTER_TENSOR
+    s = identical(rt, rows, cam, W, H, 6, seed=seed, flags=rt.FLAG_SIMT_FILTER)
+    assert np.array_equal(a[1], s[1]) and a[2].rays == s[2].rays
+    assert a[2].rays > 1.2 * a[2].samples
