@@ -34,7 +34,7 @@ struct ConstRows {
 // a wave live in the warp's shared memory; the rest of a slot's state (throughput, item sums, item)
 // lives in a pool in device memory (L2-resident).
 #ifndef RTW_LIST_SMEM
-#define RTW_LIST_SMEM 224
+#define RTW_LIST_SMEM 176  // with 176 the cover scene's CTA (operand 64 KB + 20 warp states + per-hit rows) stays under the 164 KB shared-memory step: 32 KB more L1
 #endif
 constexpr unsigned kListSmem = RTW_LIST_SMEM;   // candidate entries of a warp and wave kept in shared memory
 constexpr unsigned kListGlobalPerSlot = 64;     // ... and this many more per slot in the pool (x 64 slots per warp)
