@@ -83,3 +83,19 @@ def test_probe_masks_contain_every_exact_line_pass(rt, name):
     slack = kappa * (2 * c2 + np.abs(r * r - c2))[None, :] + ((2 * kappa + 4e-7) * o2)[:, None]
     err = np.abs(vals[:, :ns] - (e64 + slack)) / (kappa * ((2 * c2 + np.abs(r * r - c2))[None, :] + (2 * o2)[:, None]))
     assert err.max() < 0.25, err.max()  # measured 0.04
+
+
+@pytest.mark.parametrize("n", [32, 33, 63, 64, 65, 128, 129, 448, 959, 960, 961, 1024, 1025, 1344, 1345, 1537])
+def test_sphere_counts_around_tile_and_chunk_boundaries(rt, n):
+    """the cover scene tiled / truncated to n spheres: whole and ragged last tiles, the resident / streamed limit
+    (960), whole and ragged last chunks (6 tiles = 384 spheres).  Tensor cores and FFMA2 loop: same bytes."""
+    cover = golden("cover_small.npz")["spheres"]
+    reps = -(-n // len(cover))
+    rows = np.concatenate([cover] + [cover[1:] + np.array([0, 0, 30.0 * k, 0, 0, 0, 0, 0, 0]) for k in range(1, reps + 1)])[:n]
+    W, H = 80, 45
+    cam = cam_for(rt, "cover", W, H)
+    a = rt.render_image(rt.Scene(rows), cam, rt.Config(W, H, 4, 50, seed=n))
+    s = rt.render_image(rt.Scene(rows), cam, rt.Config(W, H, 4, 50, seed=n, flags=rt.FLAG_SIMT_FILTER))
+    assert a[2].filter_unit == rt.FILTER_TENSOR and s[2].filter_unit == rt.FILTER_SIMT
+    assert a[2].rays == s[2].rays
+    assert np.array_equal(a[1], s[1]) and np.array_equal(a[0], s[0])
