@@ -22,6 +22,14 @@
 //             the survivors, and the slot's closest-hit record is updated under the reference's
 //             tie rule.  Lanes are balanced by ENTRY, not by slot.
 //   bvh_trace optional replacement of filter + resolve: closest hit through the host-built BVH.
+//
+// Three kernels share these phases and differ in the filter:
+//   fused_tc_kernel   (default, 32 .. 960 spheres) the filter as a 3xTF32 contraction on the tensor cores:
+//                     filter_rays_tc, one CTA of five warpgroups per SM, sphere operand resident in shared
+//                     memory, entries name single spheres;
+//   fused_tcs_kernel  (more than 960 spheres) the same with the operand streamed through two chunk buffers;
+//   fused_kernel      the FFMA2 loop above (RT_FLAG_SIMT_FILTER, fewer than 32 spheres, RT_FLAG_NO_FILTER) and
+//                     the BVH form.
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 #include "rt_tc.cuh"
