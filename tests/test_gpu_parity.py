@@ -106,6 +106,21 @@ def test_same_stream_vs_oracle(rt, orc, name, W, H, spp):
     assert (np.abs(rgb.astype(int) - oq.astype(int)) > 1).mean() < 2e-3
 
 
+def test_same_stream_vs_oracle_streamed_operand(rt, orc):
+    """the same comparison on a scene beyond 960 spheres (the tensor-core filter streams its operand through
+    shared memory, per-hit rows come from L1/L2): 1456 spheres, same tolerances."""
+    cover = golden("cover_small.npz")["spheres"]
+    rows = np.concatenate([cover] + [cover[1:] + np.array([0, 0, 30.0 * k, 0, 0, 0, 0, 0, 0]) for k in (1, 2)])
+    W, H, spp = 64, 36, 8
+    rgb, lin, st = rt.render_image(rt.Scene(rows), cam_for(rt, "cover", W, H), rt.Config(W, H, spp, 50, seed=7))
+    assert st.filter_unit == rt.FILTER_TENSOR and len(rows) > 960
+    olin, samples, rays = orc.render(rows, orc.scene_camera("cover", W, H), W, H, spp, mode=orc.RNG_PHILOX, seed=7)
+    err = np.abs(lin / spp - olin / spp)
+    assert st.samples == samples
+    assert np.median(err) < 1e-6 and err.mean() < 5e-5
+    assert abs(st.rays - rays) / rays < 2e-3
+
+
 def test_single_sample_parity(rt, orc):
     """spp = 1 with sample_offset: every pixel is ONE path; >= 99.9 % of paths must agree with the
     f64 oracle to 1e-4 (the rest are legitimately diverged by rounding)."""
