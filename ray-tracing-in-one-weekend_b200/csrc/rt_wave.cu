@@ -945,75 +945,68 @@ fused_tc_kernel(const __grid_constant__ WaveParams P) {
 
 // ================================================================ tensor-core filter, streamed operand
 // Scenes beyond kTcMaxSpheres: the sphere operand (128 B per sphere) no longer fits a CTA's shared memory, so
-// it streams through two chunk buffers with bulk (TMA) copies.  All five warpgroups of the CTA have to look
-// at the same chunk, so the CTA runs its waves in step: shade (CTA-wide exit vote), then per ray block the
-// chunks in order -- wait for the chunk's bytes, rounds of filter_rays_tc over its tiles, a CTA barrier, and
-// one thread starts the copy of the chunk after next into the buffer just freed -- then resolve.
-#ifndef RTW_TCS_CHUNK_TILES
-#define RTW_TCS_CHUNK_TILES 6
-#endif
-constexpr uint32_t kTcsChunkTiles = RTW_TCS_CHUNK_TILES;
+// every warpgroup streams it through kTcsBufs tile buffers of its own with bulk (TMA) copies: while the MMAs of
+// tile t run, the next tiles are already in the other buffers and the copy of tile t + kTcsBufs starts as soon
+// as the group has read the accumulator of tile t (whose MMAs -- the readers of that buffer -- are then complete).
+// The group's issuer thread is the producer; the groups stay independent of each other, as in the resident form.
 constexpr uint32_t kTcsTileBytes = 4u * (uint32_t)kTcSlabFloats * 4u;  // 8 KB per 64 spheres
-constexpr uint32_t kTcsChunkBytes = kTcsChunkTiles * kTcsTileBytes;
+#ifndef RTW_TCS_BUFS
+#define RTW_TCS_BUFS 2
+#endif
+constexpr uint32_t kTcsBufs = RTW_TCS_BUFS;  // tile buffers per warpgroup (copies run kTcsBufs - 1 rounds ahead)
 
 __device__ __forceinline__ uint32_t filter_rays_tc_stream(const WaveParams &P, WarpState &W, uint32_t *glist,
                                                           const uint32_t lane, const uint32_t gid, const bool issuer,
                                                           uint64_t *bar, uint32_t &parity, const uint32_t tmem_g,
                                                           unsigned char *bufs, uint64_t *full, uint32_t &fpar) {
   const uint32_t tiles = P.scene.tc_tiles;
-  const uint32_t nchunks = (tiles + kTcsChunkTiles - 1u) / kTcsChunkTiles, visits = 2u * nchunks;
   const uint32_t lane_base = (((threadIdx.x >> 5) & 3u) * 32u) << 16;
   const uint32_t a_tmem = tmem_g, d_tmem = tmem_g + 32u;
   constexpr uint32_t gcap = 64u * kListGlobalPerSlot;
-  const bool producer = threadIdx.x == 0u;
-  // chunk of visit v (the chunks of ray block 0, then the same chunks again for block 1) -> buffer v & 1
-  auto load = [&](const uint32_t v) {
-    const uint32_t c = v < nchunks ? v : v - nchunks, b = v & 1u;
-    const uint32_t t0 = c * kTcsChunkTiles, nt = min(kTcsChunkTiles, tiles - t0), bytes = nt * kTcsTileBytes;
-    mbar_expect_tx(full + b, bytes);
-    bulk_g2s(bufs + (size_t)b * kTcsChunkBytes,
-             reinterpret_cast<const unsigned char *>(P.scene.tc_op) + (size_t)t0 * kTcsTileBytes, bytes, full + b);
+  const uint64_t desc_b0 = tc_smem_desc(bufs);
+  // producer side (issuer only): tile t of the scene -> buffer t % kTcsBufs
+  auto load = [&](const uint32_t t) {
+    const uint32_t b = t % kTcsBufs;
+    mbar_expect_tx(full + b, kTcsTileBytes);
+    bulk_g2s(bufs + (size_t)b * kTcsTileBytes,
+             reinterpret_cast<const unsigned char *>(P.scene.tc_op) + (size_t)t * kTcsTileBytes, kTcsTileBytes, full + b);
   };
-  // every warp of the CTA is past the barrier that ended the previous wave's last chunk: both buffers are free
-  if (producer) { load(0u); if (visits > 1u) load(1u); }
+  // the tile's bytes have landed, then its four K steps; bit b of fpar is the phase of buffer b
+  auto issue = [&](const uint32_t t) {
+    if (issuer) {
+      const uint32_t b = t % kTcsBufs;
+      mbar_wait(full + b, (fpar >> b) & 1u);
+      fpar ^= 1u << b;
+      tc_fence_after();
+      const uint64_t dt = desc_b0 + (uint64_t)(b * 4u) * (uint64_t)kTcSlabUnits;
+#pragma unroll
+      for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * (uint64_t)kTcSlabUnits, kTcIdesc, j);
+      tc_commit(bar);
+    }
+  };
   if (lane == 0) W.cnt = 0u;  // ordered before the first append by the group barriers below
-  uint32_t slot = lane, skip_t = 0u, keep0 = ~0u, keep1 = ~0u;
 #pragma unroll 1
-  for (uint32_t v = 0; v < visits; ++v) {
-    const uint32_t blk = v >= nchunks ? 1u : 0u, c = v - blk * nchunks, b = v & 1u;
-    if (c == 0u) {
-      // a new block of rays: features -> tensor memory (the MMAs of the block before are complete)
-      slot = lane + 32u * blk;
-      const float4 o = W.ro[slot], d = W.rd[slot];
-      const uint32_t skip = (uint32_t)__float_as_int(d.w);
-      skip_t = skip / (uint32_t)kTcTile;
-      const uint32_t skip_b = skip - skip_t * (uint32_t)kTcTile;
-      keep0 = skip_b < 32u ? ~(1u << skip_b) : ~0u;
-      keep1 = skip_b < 32u ? ~0u : ~(1u << (skip_b - 32u));
+  for (uint32_t blk = 0; blk < 2u; ++blk) {
+    // the MMAs of the block before are complete: both buffers are free
+    if (issuer)
+      for (uint32_t t = 0; t < kTcsBufs && t < tiles; ++t) load(t);
+    const uint32_t slot = lane + 32u * blk;
+    const float4 o = W.ro[slot], d = W.rd[slot];
+    const uint32_t skip = (uint32_t)__float_as_int(d.w);
+    const uint32_t skip_t = skip / (uint32_t)kTcTile, skip_b = skip - skip_t * (uint32_t)kTcTile;
+    const uint32_t keep0 = skip_b < 32u ? ~(1u << skip_b) : ~0u;
+    const uint32_t keep1 = skip_b < 32u ? ~0u : ~(1u << (skip_b - 32u));
+    {
       uint32_t sv[kTcK];
       tc_ray_slots(o, d, sv);
       TC_ST32(a_tmem + lane_base, sv);
-      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-      tc_fence_before();
-      group_sync(gid);
     }
-    // the chunk's bytes have landed (bulk copy -> mbarrier); parity bit b of fpar is buffer b's phase
-    mbar_wait(full + b, (fpar >> b) & 1u);
-    fpar ^= 1u << b;
-    const uint32_t t0 = c * kTcsChunkTiles, nt = min(kTcsChunkTiles, tiles - t0);
-    const uint64_t desc0 = tc_smem_desc(bufs + (size_t)b * kTcsChunkBytes);
-    auto issue = [&](const uint32_t t) {
-      if (issuer) {
-        tc_fence_after();
-        const uint64_t dt = desc0 + (uint64_t)(t * 4u) * (uint64_t)kTcSlabUnits;
-#pragma unroll
-        for (uint32_t j = 0; j < 4u; ++j) tc_mma_ts(d_tmem, a_tmem + j * 8u, dt + (uint64_t)j * (uint64_t)kTcSlabUnits, kTcIdesc, j);
-        tc_commit(bar);
-      }
-    };
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    tc_fence_before();
+    group_sync(gid);
     issue(0u);
 #pragma unroll 1
-    for (uint32_t t = 0; t < nt; ++t) {
+    for (uint32_t t = 0; t < tiles; ++t) {
       if (!(parity & 0x80000000u) && !mbar_wait_bounded(bar, parity & 1u)) {
         atomicExch(P.status, 1u);
         parity |= 0x80000000u;
@@ -1029,11 +1022,12 @@ __device__ __forceinline__ uint32_t filter_rays_tc_stream(const WaveParams &P, W
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       tc_fence_before();
       group_sync(gid);
-      if (t + 1u < nt) issue(t + 1u);
+      // D is free and the MMAs of tile t are complete: their buffer takes tile t + 2, tile t + 1 starts
+      if (issuer && t + kTcsBufs < tiles) load(t + kTcsBufs);
+      if (t + 1u < tiles) issue(t + 1u);
       p1 = tc_pass_bits_hi(vv);
-      const uint32_t tg = t0 + t;  // tile of the scene
-      if (tg == skip_t) { p0 &= keep0; p1 &= keep1; }
-      const uint32_t ebase = (slot << kGroupBits) + tg * (uint32_t)kTcTile;
+      if (t == skip_t) { p0 &= keep0; p1 &= keep1; }
+      const uint32_t ebase = (slot << kGroupBits) + t * (uint32_t)kTcTile;
       if ((p0 | p1) != 0u) {
         uint32_t pos = atomicAdd(&W.cnt, (uint32_t)(__popc(p0) + __popc(p1)));
         auto put = [&](uint32_t p, const uint32_t eb) {
@@ -1049,9 +1043,6 @@ __device__ __forceinline__ uint32_t filter_rays_tc_stream(const WaveParams &P, W
         put(p1, ebase + 32u);
       }
     }
-    // every warpgroup has waited for its last MMA on this buffer: it may be refilled
-    __syncthreads();
-    if (producer && v + 2u < visits) load(v + 2u);
   }
   __syncwarp();
   return W.cnt;
@@ -1062,12 +1053,14 @@ __global__ void __launch_bounds__(kTcBlock, 1)
 fused_tcs_kernel(const __grid_constant__ WaveParams P) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t s_mma[kTcGroups];
-  __shared__ __align__(8) uint64_t s_full[2];
+  __shared__ __align__(8) uint64_t s_full[kTcGroups][kTcsBufs];
   __shared__ uint32_t s_tmem;
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, gid = warp >> 2;
-  WarpState &W = reinterpret_cast<WarpState *>(smem_raw + 2u * kTcsChunkBytes)[warp];
-  if (threadIdx.x < kTcGroups) mbar_init(&s_mma[threadIdx.x], 1);
-  if (threadIdx.x < 2u) mbar_init(&s_full[threadIdx.x], 1);
+  WarpState &W = reinterpret_cast<WarpState *>(smem_raw + (size_t)kTcGroups * kTcsBufs * kTcsTileBytes)[warp];
+  if (threadIdx.x < kTcGroups) {
+    mbar_init(&s_mma[threadIdx.x], 1);
+    for (uint32_t b = 0; b < kTcsBufs; ++b) mbar_init(&s_full[threadIdx.x][b], 1);
+  }
   if (warp == 0) tmem_alloc(&s_tmem, 512);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the barriers are seen by the bulk copies
   const double4 *exact = P.scene.exact;
@@ -1094,15 +1087,17 @@ fused_tcs_kernel(const __grid_constant__ WaveParams P) {
     W.key[slot] = kInfKey;
     W.id[slot] = -1;
   }
+  unsigned char *bufs = smem_raw + (size_t)gid * kTcsBufs * kTcsTileBytes;
   uint32_t parity = 0, fpar = 0;
   for (;;) {
     uint32_t live = 0;
 #pragma unroll 1
     for (int r = 0; r < 2; ++r)
       live += shade_slot<F32HIT>(P, W, lane + 32u * r, base + r * stride, exact, mat, aux, npix, total_items);
-    if (!__syncthreads_or((int)(live != 0u))) break;  // the CTA's waves run in step: it leaves as one
+    if (!group_or(gid, live != 0u)) break;  // the four warps of a group leave together
+    __syncwarp();
     const uint32_t n_entries = filter_rays_tc_stream(P, W, glist, lane, gid, issuer, &s_mma[gid], parity, tmem_g,
-                                                     smem_raw, s_full, fpar);
+                                                     bufs, s_full[gid], fpar);
     __syncwarp();
     if (n_entries <= kListSmem + 64u * kListGlobalPerSlot) resolve_entries<RTW_G, F32HIT, true>(P, W, glist, n_entries, exact, lane);
     else resolve_scan<F32HIT>(P, W, exact, lane);
@@ -1198,10 +1193,10 @@ static cudaError_t launch_fused_tc(WaveParams &p, void *pool, uint32_t pool_slot
   return cudaGetLastError();
 }
 
-// streamed form: two chunk buffers | warp states (the per-hit rows stay in L1/L2)
+// streamed form: two tile buffers per warpgroup | warp states (the per-hit rows stay in L1/L2)
 static cudaError_t launch_fused_tcs(WaveParams &p, void *pool, uint32_t pool_slots, bool f32hit, int sm_count,
                                     size_t smem_optin_max, int *grid_out, cudaStream_t st) {
-  const size_t smem = 2u * (size_t)kTcsChunkBytes + (size_t)kTcWarps * sizeof(WarpState);
+  const size_t smem = (size_t)kTcGroups * kTcsBufs * kTcsTileBytes + (size_t)kTcWarps * sizeof(WarpState);
   if (smem > smem_optin_max) return cudaErrorInvalidValue;
   const int grid = sm_count;
   const uint32_t n_slots = (uint32_t)grid * kTcBlock * 2u;
